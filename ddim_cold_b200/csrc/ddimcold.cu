@@ -1,0 +1,640 @@
+// C-ABI implementation (include/ddimcold.h): plan, weight packing, the step schedule, the
+// per-step kernel chain and its CUDA-graph replay.  Device memory always belongs to the
+// caller; this file owns only host structs, TMA descriptors and graph objects.
+#include "../../include/ddimcold.h"
+
+#include <math.h>
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "attention.cuh"
+#include "common.cuh"
+#include "elementwise.cuh"
+#include "gemm_umma.cuh"
+
+using namespace ddc;
+
+static_assert(sizeof(ddc_step) == sizeof(StepEntry), "host/device step entry mismatch");
+
+// ------------------------------------------------------------------------------- errors
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CK(call)                                                                                        \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess)                                                                          \
+            return fail(DDC_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+#define TRY(call)            \
+    do {                     \
+        int r_ = (call);     \
+        if (r_ != DDC_OK) return r_; \
+    } while (0)
+
+extern "C" const char* ddc_last_error(void) { return g_err.c_str(); }
+extern "C" int ddc_version(void) { return 100; }
+
+// ------------------------------------------------------------------------------- TMA descriptors
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int get_encode_fn(EncodeTiledFn* out) {
+    static EncodeTiledFn fn = nullptr;
+    if (fn == nullptr) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+        if (p == nullptr || qres != cudaDriverEntryPointSuccess)
+            return fail(DDC_E_CUDA, "cuTensorMapEncodeTiled not available from this driver");
+        fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    *out = fn;
+    return DDC_OK;
+}
+
+// bf16 [rows, cols] row-major, box = 64 columns x box_rows rows, 128-byte swizzle
+static int make_tmap(CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+    EncodeTiledFn enc;
+    TRY(get_encode_fn(&enc));
+    if (cols % 64 != 0 || box_rows == 0 || box_rows > 256 || (reinterpret_cast<uintptr_t>(base) & 0xF) != 0)
+        return fail(DDC_E_INVALID, "tensor map: cols=%llu box_rows=%u base=%p", (unsigned long long)cols, box_rows, base);
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {cols * 2};
+    cuuint32_t box[2] = {64, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(DDC_E_CUDA, "cuTensorMapEncodeTiled -> %d", static_cast<int>(r));
+    return DDC_OK;
+}
+
+// ------------------------------------------------------------------------------- GEMM launch
+static int pick_bn(int N) {
+    const int cands[] = {128, 96, 64, 48, 32, 16};
+    for (int c : cands)
+        if (N % c == 0) return c;
+    return 0;
+}
+
+static int pick_stages(int K, int bn) {
+    const size_t budget = 200 * 1024;
+    const size_t a = static_cast<size_t>(K / GEMM_BK) * GEMM_A_KBLOCK_BYTES;
+    int s = static_cast<int>((budget - a) / (static_cast<size_t>(bn) * 128));
+    if (s > 6) s = 6;
+    return s;
+}
+
+template <int AMODE, int EPI>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams p, cudaStream_t st) {
+    static int attr_dev_mask = 0;   // bit per device where the smem attribute has been raised
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (!(attr_dev_mask & (1 << dev))) {
+        CK(cudaFuncSetAttribute(gemm_umma_kernel<AMODE, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_dev_mask |= (1 << dev);
+    }
+    if (p.K % GEMM_BK != 0 || p.K > 512 || p.bn % 16 != 0 || p.bn > 256 || p.N % p.bn != 0 || p.stages < 2)
+        return fail(DDC_E_INVALID, "gemm: unsupported M=%d N=%d K=%d bn=%d stages=%d", p.M, p.N, p.K, p.bn, p.stages);
+    const size_t smem = gemm_smem_bytes(p.K, p.bn, p.stages);
+    if (smem > 227 * 1024) return fail(DDC_E_INVALID, "gemm: %zu B of shared memory needed", smem);
+    const int grid = (p.M + GEMM_BM - 1) / GEMM_BM;
+    gemm_umma_kernel<AMODE, EPI><<<grid, GEMM_THREADS, smem, st>>>(tmA, tmB, p);
+    CK(cudaGetLastError());
+    return DDC_OK;
+}
+
+// ------------------------------------------------------------------------------- attention launch
+static int att_pick_kc(int L) {
+    const int cands[] = {128, 96, 80, 64, 48, 32};
+    int best = 0, best_pad = 1 << 30;
+    for (int c : cands) {
+        const int pad = (L + c - 1) / c * c;
+        if (pad < best_pad) { best_pad = pad; best = c; }
+    }
+    return best;
+}
+
+template <int D, int KC>
+static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads, cudaStream_t st) {
+    static int attr_dev_mask = 0;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    const size_t smem = att_smem_bytes(L, D, KC);
+    if (smem > 227 * 1024) return fail(DDC_E_INVALID, "attention: L=%d needs %zu B of shared memory", L, smem);
+    if (!(attr_dev_mask & (1 << dev))) {
+        CK(cudaFuncSetAttribute(attention_kernel<D, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_dev_mask |= (1 << dev);
+    }
+    int warps = (L + 15) / 16;
+    if (warps > ATT_MAX_WARPS) warps = ATT_MAX_WARPS;
+    const float scale_log2e = (1.0f / sqrtf(static_cast<float>(D))) * 1.44269504088896340736f;
+    attention_kernel<D, KC><<<dim3(heads, B), warps * 32, smem, st>>>(qkv, out, L, C, scale_log2e);
+    CK(cudaGetLastError());
+    return DDC_OK;
+}
+
+static int run_attention(const bf16* qkv, bf16* out, int B, int L, int C, int heads, cudaStream_t st) {
+    if (heads <= 0 || C % heads != 0) return fail(DDC_E_INVALID, "attention: C=%d heads=%d", C, heads);
+    const int D = C / heads;
+    const int kc = att_pick_kc(L);
+#define ATT_CASE(DD, KK) \
+    if (D == DD && kc == KK) return launch_att<DD, KK>(qkv, out, B, L, C, heads, st);
+    ATT_CASE(32, 128) ATT_CASE(32, 96) ATT_CASE(32, 80) ATT_CASE(32, 64) ATT_CASE(32, 48) ATT_CASE(32, 32)
+    ATT_CASE(64, 128) ATT_CASE(64, 96) ATT_CASE(64, 80) ATT_CASE(64, 64) ATT_CASE(64, 48) ATT_CASE(64, 32)
+#undef ATT_CASE
+    return fail(DDC_E_INVALID, "attention: head_dim %d unsupported (32 or 64)", D);
+}
+
+// ------------------------------------------------------------------------------- plan
+struct LayerW {
+    float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *b_qkv, *b_proj, *b_fc1, *b_fc2;
+    bf16 *w_qkv, *w_proj, *w_fc1, *w_fc2;
+    CUtensorMap tm_qkv, tm_proj, tm_fc1, tm_fc2;
+};
+
+struct GraphKey {
+    int B;
+    const void *x, *x0_last, *x0_seq, *eps_seq;
+    bool operator==(const GraphKey& o) const {
+        return B == o.B && x == o.x && x0_last == o.x0_last && x0_seq == o.x0_seq && eps_seq == o.eps_seq;
+    }
+};
+
+struct ddc_plan {
+    ddc_shape sh;
+    int maxB, device;
+    int L, n, P, C, Kp, Mpad;
+    int bn_qkv, bn_c, bn_head;
+    bool packed;
+    // weight arena
+    bf16* w_patch;
+    float* posb;
+    float* time_tab;
+    std::vector<LayerW> layers;
+    float *lnf_g, *lnf_b, *b_head;
+    bf16* w_head;
+    CUtensorMap tm_wpatch, tm_whead;
+    // work arena
+    float* X;
+    bf16 *QKV, *O, *Hd, *Ap;
+    float* Y;
+    StepEntry* tbl;
+    int* ctr;
+    CUtensorMap tm_Ap, tm_O, tm_Hd;
+    // graph cache
+    cudaGraphExec_t gexec;
+    GraphKey gkey;
+};
+
+struct Carver {
+    char* base;
+    size_t off;
+    template <typename T>
+    T* take(size_t n) {
+        off = (off + 255) & ~static_cast<size_t>(255);
+        T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+        off += n * sizeof(T);
+        return p;
+    }
+};
+
+static int check_shape(const ddc_shape* s, int max_batch) {
+    if (s == nullptr) return fail(DDC_E_INVALID, "shape is NULL");
+    if (s->in_chans != 3) return fail(DDC_E_INVALID, "in_chans must be 3 (got %d)", s->in_chans);
+    if (s->patch <= 0 || s->patch % 2 != 0 || s->img_h % s->patch != 0 || s->img_w % s->patch != 0)
+        return fail(DDC_E_INVALID, "patch %d must be even and divide the image %dx%d", s->patch, s->img_h, s->img_w);
+    if (s->embed % 64 != 0 || s->embed > 512 || s->embed <= 0)
+        return fail(DDC_E_INVALID, "embed_dim %d must be a multiple of 64 and <= 512", s->embed);
+    if (s->heads <= 0 || s->embed % s->heads != 0 || (s->embed / s->heads != 32 && s->embed / s->heads != 64))
+        return fail(DDC_E_INVALID, "head_dim = %d/%d must be 32 or 64", s->embed, s->heads);
+    if (s->depth <= 0 || s->total_steps <= 0 || max_batch <= 0) return fail(DDC_E_INVALID, "depth/total_steps/max_batch");
+    const int P = 3 * s->patch * s->patch;
+    if (P % 16 != 0 || ((P + 63) / 64 * 64) > 512) return fail(DDC_E_INVALID, "patch dim %d unsupported", P);
+    return DDC_OK;
+}
+
+static void carve(ddc_plan* pl, void* weight_arena, void* work_arena, size_t* wbytes, size_t* kbytes) {
+    const ddc_shape& s = pl->sh;
+    const size_t C = pl->C, L = pl->L, P = pl->P, Kp = pl->Kp, Mp = pl->Mpad;
+    Carver w{static_cast<char*>(weight_arena), 0};
+    pl->w_patch = w.take<bf16>(C * Kp);
+    pl->posb = w.take<float>(L * C);
+    pl->time_tab = w.take<float>(static_cast<size_t>(s.total_steps) * C);
+    pl->layers.resize(s.depth);
+    for (auto& l : pl->layers) {
+        l.ln1_g = w.take<float>(C);  l.ln1_b = w.take<float>(C);
+        l.w_qkv = w.take<bf16>(3 * C * C);  l.b_qkv = w.take<float>(3 * C);
+        l.w_proj = w.take<bf16>(C * C);  l.b_proj = w.take<float>(C);
+        l.ln2_g = w.take<float>(C);  l.ln2_b = w.take<float>(C);
+        l.w_fc1 = w.take<bf16>(C * C);  l.b_fc1 = w.take<float>(C);
+        l.w_fc2 = w.take<bf16>(C * C);  l.b_fc2 = w.take<float>(C);
+    }
+    pl->lnf_g = w.take<float>(C);
+    pl->lnf_b = w.take<float>(C);
+    pl->w_head = w.take<bf16>(P * C);
+    pl->b_head = w.take<float>(P);
+    *wbytes = (w.off + 255) & ~static_cast<size_t>(255);
+
+    Carver k{static_cast<char*>(work_arena), 0};
+    pl->X = k.take<float>(Mp * C);
+    pl->QKV = k.take<bf16>(Mp * 3 * C);
+    pl->O = k.take<bf16>(Mp * C);
+    pl->Hd = k.take<bf16>(Mp * C);
+    pl->Ap = k.take<bf16>(Mp * Kp);
+    pl->Y = k.take<float>(Mp * P);
+    pl->tbl = k.take<StepEntry>(s.total_steps);
+    pl->ctr = k.take<int>(64);
+    *kbytes = (k.off + 255) & ~static_cast<size_t>(255);
+}
+
+static void derive(ddc_plan* pl, const ddc_shape* s, int max_batch) {
+    pl->sh = *s;
+    pl->maxB = max_batch;
+    pl->n = (s->img_h / s->patch) * (s->img_w / s->patch);
+    pl->L = pl->n + 1;
+    pl->P = 3 * s->patch * s->patch;
+    pl->C = s->embed;
+    pl->Kp = (pl->P + 63) / 64 * 64;
+    pl->Mpad = (max_batch * pl->L + GEMM_BM - 1) / GEMM_BM * GEMM_BM;
+    pl->bn_qkv = pick_bn(3 * pl->C);
+    pl->bn_c = pick_bn(pl->C);
+    pl->bn_head = pick_bn(pl->P);
+}
+
+extern "C" int ddc_arena_bytes(const ddc_shape* shape, int32_t max_batch, size_t* weight_bytes, size_t* work_bytes) {
+    TRY(check_shape(shape, max_batch));
+    ddc_plan tmp{};
+    derive(&tmp, shape, max_batch);
+    size_t w = 0, k = 0;
+    carve(&tmp, nullptr, nullptr, &w, &k);
+    if (weight_bytes) *weight_bytes = w;
+    if (work_bytes) *work_bytes = k;
+    return DDC_OK;
+}
+
+extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_t device, void* weight_arena,
+                               size_t weight_bytes, void* work_arena, size_t work_bytes, ddc_plan** out) {
+    if (out == nullptr) return fail(DDC_E_INVALID, "out is NULL");
+    *out = nullptr;
+    TRY(check_shape(shape, max_batch));
+    if (weight_arena == nullptr || work_arena == nullptr) return fail(DDC_E_INVALID, "arena pointer is NULL");
+    if ((reinterpret_cast<uintptr_t>(weight_arena) | reinterpret_cast<uintptr_t>(work_arena)) & 255)
+        return fail(DDC_E_INVALID, "arenas must be 256-byte aligned");
+    CK(cudaSetDevice(device));
+    int major = 0, minor = 0;
+    CK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    CK(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, device));
+    if (major != 10)
+        return fail(DDC_E_CUDA, "device %d is sm_%d%d; this library contains sm_100a code only", device, major, minor);
+    ddc_plan* pl = new ddc_plan();
+    derive(pl, shape, max_batch);
+    pl->device = device;
+    pl->packed = false;
+    pl->gexec = nullptr;
+    pl->gkey = GraphKey{0, nullptr, nullptr, nullptr, nullptr};
+    size_t w = 0, k = 0;
+    carve(pl, weight_arena, work_arena, &w, &k);
+    if (w > weight_bytes || k > work_bytes) {
+        delete pl;
+        return fail(DDC_E_STATE, "arena too small: need %zu/%zu B, got %zu/%zu B", w, k, weight_bytes, work_bytes);
+    }
+    const uint64_t C = pl->C, Mp = pl->Mpad;
+    int r = DDC_OK;
+    auto mk = [&](CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint32_t box) {
+        if (r == DDC_OK) r = make_tmap(m, base, rows, cols, box);
+    };
+    mk(&pl->tm_Ap, pl->Ap, Mp, pl->Kp, GEMM_BM);
+    mk(&pl->tm_O, pl->O, Mp, C, GEMM_BM);
+    mk(&pl->tm_Hd, pl->Hd, Mp, C, GEMM_BM);
+    mk(&pl->tm_wpatch, pl->w_patch, C, pl->Kp, pl->bn_c);
+    mk(&pl->tm_whead, pl->w_head, pl->P, C, pl->bn_head);
+    for (auto& l : pl->layers) {
+        mk(&l.tm_qkv, l.w_qkv, 3 * C, C, pl->bn_qkv);
+        mk(&l.tm_proj, l.w_proj, C, C, pl->bn_c);
+        mk(&l.tm_fc1, l.w_fc1, C, C, pl->bn_c);
+        mk(&l.tm_fc2, l.w_fc2, C, C, pl->bn_c);
+    }
+    if (r != DDC_OK) {
+        delete pl;
+        return r;
+    }
+    *out = pl;
+    return DDC_OK;
+}
+
+extern "C" int ddc_plan_destroy(ddc_plan* plan) {
+    if (plan == nullptr) return DDC_OK;
+    if (plan->gexec) cudaGraphExecDestroy(plan->gexec);
+    delete plan;
+    return DDC_OK;
+}
+
+extern "C" int ddc_launches_per_step(const ddc_plan* plan) {
+    if (plan == nullptr) return 0;
+    return 2 + 5 * plan->sh.depth + 2;   // patchify, embed GEMM, 5 per block, head GEMM, head_ddim
+}
+
+// ------------------------------------------------------------------------------- packing
+extern "C" int ddc_pack_weights(ddc_plan* pl, const float* const* t, int32_t n_tensors, void* stream) {
+    if (pl == nullptr || t == nullptr) return fail(DDC_E_INVALID, "NULL argument");
+    const int expect = 9 + 12 * pl->sh.depth;
+    if (n_tensors != expect) return fail(DDC_E_INVALID, "expected %d state_dict tensors, got %d", expect, n_tensors);
+    for (int i = 0; i < n_tensors; ++i)
+        if (t[i] == nullptr) return fail(DDC_E_INVALID, "state_dict tensor %d is NULL", i);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(pl->device));
+    const int C = pl->C, L = pl->L, P = pl->P;
+    auto pack = [&](const float* src, bf16* dst, int rows, int cols, int cols_pad) {
+        pack_bf16_kernel<<<296, 256, 0, st>>>(src, dst, rows, cols, cols_pad);
+    };
+    auto copy = [&](const float* src, float* dst, size_t n) { copy_f32_kernel<<<148, 256, 0, st>>>(src, dst, n); };
+    const float* cls = t[0];
+    const float* pos = t[1];
+    pack(t[2], pl->w_patch, C, P, pl->Kp);
+    pack_posb_kernel<<<148, 256, 0, st>>>(pos, cls, t[3], pl->posb, L, C);
+    copy(t[4], pl->time_tab, static_cast<size_t>(pl->sh.total_steps) * C);
+    for (int i = 0; i < pl->sh.depth; ++i) {
+        const float* const* b = t + 5 + 12 * i;
+        LayerW& l = pl->layers[i];
+        copy(b[0], l.ln1_g, C);  copy(b[1], l.ln1_b, C);
+        pack(b[2], l.w_qkv, 3 * C, C, C);  copy(b[3], l.b_qkv, 3 * C);
+        pack(b[4], l.w_proj, C, C, C);  copy(b[5], l.b_proj, C);
+        copy(b[6], l.ln2_g, C);  copy(b[7], l.ln2_b, C);
+        pack(b[8], l.w_fc1, C, C, C);  copy(b[9], l.b_fc1, C);
+        pack(b[10], l.w_fc2, C, C, C);  copy(b[11], l.b_fc2, C);
+    }
+    const float* const* e = t + 5 + 12 * pl->sh.depth;
+    copy(e[0], pl->lnf_g, C);  copy(e[1], pl->lnf_b, C);
+    pack(e[2], pl->w_head, P, C, C);  copy(e[3], pl->b_head, P);
+    CK(cudaGetLastError());
+    pl->packed = true;
+    return DDC_OK;
+}
+
+// ------------------------------------------------------------------------------- one predictor evaluation
+// Enqueues: patchify -> embed GEMM -> depth x [LN1+qkv GEMM, attention, proj GEMM(+res),
+// LN2+fc1 GEMM(+GELU), fc2 GEMM(+res)] -> LN+head GEMM.  Leaves the head output in pl->Y.
+static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_img, bool use_step_ctr, cudaStream_t st) {
+    const ddc_shape& s = pl->sh;
+    const int C = pl->C, L = pl->L, M = B * L;
+    patchify_kernel<<<dim3(s.img_h / s.patch, B), 256, 0, st>>>(x, pl->Ap, s.img_h, s.img_w, s.patch, L, pl->Kp,
+                                                                  use_step_ctr ? pl->ctr : nullptr);
+    CK(cudaGetLastError());
+    GemmParams g{};
+    g.M = M;
+    g.ln_eps = 1e-5f;
+    // patch embed + cls/pos/time
+    g.N = C; g.K = pl->Kp; g.bn = pl->bn_c; g.stages = pick_stages(g.K, g.bn);
+    g.out_f32 = pl->X; g.ld_f32 = C;
+    g.posb = pl->posb; g.L = L; g.time_tab = pl->time_tab; g.t_img = t_img; g.tbl = pl->tbl; g.cur = pl->ctr;
+    TRY((launch_gemm<A_TMA, EPI_EMBED>(pl->tm_Ap, pl->tm_wpatch, g, st)));
+    for (int i = 0; i < s.depth; ++i) {
+        LayerW& l = pl->layers[i];
+        GemmParams q{};
+        q.M = M; q.ln_eps = 1e-5f;
+        q.N = 3 * C; q.K = C; q.bn = pl->bn_qkv; q.stages = pick_stages(q.K, q.bn);
+        q.x = pl->X; q.ldx = C; q.ln_g = l.ln1_g; q.ln_b = l.ln1_b;
+        q.bias = l.b_qkv; q.out_bf16 = pl->QKV; q.ld_bf16 = 3 * C;
+        TRY((launch_gemm<A_LN, EPI_BF16>(l.tm_qkv, l.tm_qkv, q, st)));
+        TRY(run_attention(pl->QKV, pl->O, B, L, C, s.heads, st));
+        GemmParams r{};
+        r.M = M; r.N = C; r.K = C; r.bn = pl->bn_c; r.stages = pick_stages(r.K, r.bn);
+        r.bias = l.b_proj; r.out_f32 = pl->X; r.ld_f32 = C;
+        TRY((launch_gemm<A_TMA, EPI_RESID>(pl->tm_O, l.tm_proj, r, st)));
+        GemmParams f{};
+        f.M = M; f.ln_eps = 1e-5f; f.N = C; f.K = C; f.bn = pl->bn_c; f.stages = pick_stages(f.K, f.bn);
+        f.x = pl->X; f.ldx = C; f.ln_g = l.ln2_g; f.ln_b = l.ln2_b;
+        f.bias = l.b_fc1; f.out_bf16 = pl->Hd; f.ld_bf16 = C;
+        TRY((launch_gemm<A_LN, EPI_BF16_GELU>(l.tm_fc1, l.tm_fc1, f, st)));
+        r.bias = l.b_fc2;
+        TRY((launch_gemm<A_TMA, EPI_RESID>(pl->tm_Hd, l.tm_fc2, r, st)));
+    }
+    GemmParams h{};
+    h.M = M; h.ln_eps = 1e-5f; h.N = pl->P; h.K = C; h.bn = pl->bn_head; h.stages = pick_stages(h.K, h.bn);
+    h.x = pl->X; h.ldx = C; h.ln_g = pl->lnf_g; h.ln_b = pl->lnf_b;
+    h.bias = pl->b_head; h.out_f32 = pl->Y; h.ld_f32 = pl->P;
+    TRY((launch_gemm<A_LN, EPI_F32>(pl->tm_whead, pl->tm_whead, h, st)));
+    return DDC_OK;
+}
+
+static size_t head_ddim_smem(const ddc_shape& s) {
+    return static_cast<size_t>(s.img_w / s.patch) * (3 * s.patch * s.patch + 1) * sizeof(float);
+}
+
+static int check_call(ddc_plan* pl, int batch) {
+    if (pl == nullptr) return fail(DDC_E_INVALID, "plan is NULL");
+    if (!pl->packed) return fail(DDC_E_STATE, "ddc_pack_weights has not been called on this plan");
+    if (batch <= 0 || batch > pl->maxB) return fail(DDC_E_INVALID, "batch %d outside 1..%d", batch, pl->maxB);
+    return DDC_OK;
+}
+
+extern "C" int ddc_forward(ddc_plan* pl, const float* x, const int32_t* t, int32_t batch, float* out, void* stream) {
+    TRY(check_call(pl, batch));
+    if (x == nullptr || t == nullptr || out == nullptr) return fail(DDC_E_INVALID, "NULL tensor");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(pl->device));
+    TRY(enqueue_predictor(pl, x, batch, t, false, st));
+    HeadDdimParams q{};
+    q.y = pl->Y; q.ldy = pl->P; q.x = out;
+    q.H = pl->sh.img_h; q.W = pl->sh.img_w; q.p = pl->sh.patch; q.L = pl->L; q.B = batch;
+    head_ddim_kernel<MODE_FORWARD><<<dim3(q.H / q.p, batch), 256, head_ddim_smem(pl->sh), st>>>(q);
+    CK(cudaGetLastError());
+    return DDC_OK;
+}
+
+static int enqueue_step(ddc_plan* pl, float* x, int B, float* x0_last, float* x0_seq, float* eps_seq, cudaStream_t st) {
+    TRY(enqueue_predictor(pl, x, B, nullptr, true, st));
+    HeadDdimParams q{};
+    q.y = pl->Y; q.ldy = pl->P; q.x = x;
+    q.H = pl->sh.img_h; q.W = pl->sh.img_w; q.p = pl->sh.patch; q.L = pl->L; q.B = B;
+    q.tbl = pl->tbl; q.cur = pl->ctr;
+    q.x0_last = x0_last; q.x0_seq = x0_seq; q.eps_seq = eps_seq;
+    head_ddim_kernel<MODE_STEP><<<dim3(q.H / q.p, B), 256, head_ddim_smem(pl->sh), st>>>(q);
+    CK(cudaGetLastError());
+    return DDC_OK;
+}
+
+extern "C" int ddc_sample(ddc_plan* pl, float* x, int32_t batch, const ddc_step* host_table, int32_t n_steps,
+                          float* x0_last, float* x0_seq, float* eps_seq, int32_t use_graph, void* stream) {
+    TRY(check_call(pl, batch));
+    if (x == nullptr || host_table == nullptr) return fail(DDC_E_INVALID, "NULL tensor");
+    if (n_steps <= 0 || n_steps > pl->sh.total_steps)
+        return fail(DDC_E_INVALID, "n_steps %d outside 1..%d", n_steps, pl->sh.total_steps);
+    for (int i = 0; i < n_steps; ++i)
+        if (host_table[i].t < 0 || host_table[i].t >= pl->sh.total_steps)
+            return fail(DDC_E_INVALID, "step %d: t=%d outside the time_embed table", i, host_table[i].t);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(pl->device));
+    // pageable-source async copies are staged before returning, so host_table may be freed by the caller
+    CK(cudaMemcpyAsync(pl->tbl, host_table, sizeof(StepEntry) * n_steps, cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(pl->ctr, 0, 2 * sizeof(int), st));
+    if (!use_graph) {
+        for (int i = 0; i < n_steps; ++i) TRY(enqueue_step(pl, x, batch, x0_last, x0_seq, eps_seq, st));
+        return DDC_OK;
+    }
+    if (st == nullptr) return fail(DDC_E_INVALID, "graph replay needs a non-default stream (capture is illegal on stream 0)");
+    const GraphKey key{batch, x, x0_last, x0_seq, eps_seq};
+    if (pl->gexec == nullptr || !(pl->gkey == key)) {
+        if (pl->gexec) {
+            cudaGraphExecDestroy(pl->gexec);
+            pl->gexec = nullptr;
+        }
+        cudaGraph_t graph = nullptr;
+        CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        const int r = enqueue_step(pl, x, batch, x0_last, x0_seq, eps_seq, st);
+        const cudaError_t e = cudaStreamEndCapture(st, &graph);
+        if (r != DDC_OK) {
+            if (graph) cudaGraphDestroy(graph);
+            return r;
+        }
+        if (e != cudaSuccess) return fail(DDC_E_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(e));
+        const cudaError_t ei = cudaGraphInstantiate(&pl->gexec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ei != cudaSuccess) {
+            pl->gexec = nullptr;
+            return fail(DDC_E_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ei));
+        }
+        pl->gkey = key;
+    }
+    for (int i = 0; i < n_steps; ++i) CK(cudaGraphLaunch(pl->gexec, st));
+    return DDC_OK;
+}
+
+// ------------------------------------------------------------------------------- schedules (host)
+extern "C" int ddc_ddim_table(int32_t k, int32_t total_steps, int32_t t_start, ddc_step* tab, int32_t capacity,
+                              int32_t* n_steps) {
+    if (tab == nullptr || n_steps == nullptr) return fail(DDC_E_INVALID, "NULL argument");
+    if (k <= 0 || total_steps <= 0 || t_start < 0 || t_start >= total_steps)
+        return fail(DDC_E_INVALID, "k=%d total_steps=%d t_start=%d", k, total_steps, t_start);
+    const double T = static_cast<double>(total_steps);
+    int n = 0;
+    for (int t = t_start; t > 0; t -= k) {
+        if (t + 1 - k < 0) return fail(DDC_E_DOMAIN, "math domain error");          // sqrt(<0) at ViT.py:231
+        const double a_tk = 1.0 - sqrt((t + 1 - k) / T);
+        const double a_t = 1.0 - sqrt((t + 1) / T) + 1e-5;
+        if (a_t <= 0.0 || a_t >= 1.0) return fail(DDC_E_DOMAIN, "math domain error");
+        if (a_tk == 0.0) return fail(DDC_E_DOMAIN, "float division by zero");        // ViT.py:234 (1-a_tk)/a_tk
+        if (a_tk < 0.0) return fail(DDC_E_DOMAIN, "math domain error");
+        if (n >= capacity) return fail(DDC_E_INVALID, "table capacity %d too small", capacity);
+        const double A = sqrt(1.0 - a_tk) / sqrt(1.0 - a_t);
+        const double Bc = sqrt(a_tk) - A * sqrt(a_t);
+        ddc_step e;
+        memset(&e, 0, sizeof(e));
+        e.t = t;
+        e.a = static_cast<float>(A);
+        e.b = static_cast<float>(Bc);
+        e.sqrt_at = static_cast<float>(sqrt(a_t));
+        e.inv_sqrt_1mat = static_cast<float>(1.0 / sqrt(1.0 - a_t));
+        tab[n++] = e;
+    }
+    if (n == 0) return fail(DDC_E_INVALID, "empty schedule");
+    tab[n - 1].flags |= 1;
+    *n_steps = n;
+    return DDC_OK;
+}
+
+extern "C" int ddc_cold_table(ddc_step* tab, int32_t capacity, int32_t* n_steps) {
+    if (tab == nullptr || n_steps == nullptr) return fail(DDC_E_INVALID, "NULL argument");
+    if (capacity < 6) return fail(DDC_E_INVALID, "table capacity %d too small", capacity);
+    for (int i = 0; i < 6; ++i) {
+        memset(&tab[i], 0, sizeof(ddc_step));
+        tab[i].t = 6 - i;
+        tab[i].a = 0.f;
+        tab[i].b = 1.f;                 // x <- clamp(f(x, t))
+        tab[i].sqrt_at = 1.f;
+        tab[i].inv_sqrt_1mat = 1.f;
+    }
+    tab[5].flags |= 1;
+    *n_steps = 6;
+    return DDC_OK;
+}
+
+// ------------------------------------------------------------------------------- kernel-level entries
+extern "C" int ddc_k_gemm(int32_t amode, int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const float* ln_g,
+                          const float* ln_b, const void* W, const float* bias, void* out, int32_t ld_out, void* stream) {
+    if (A == nullptr || W == nullptr || bias == nullptr || out == nullptr) return fail(DDC_E_INVALID, "NULL tensor");
+    if (M <= 0 || N <= 0 || K <= 0) return fail(DDC_E_INVALID, "bad sizes");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int bn = pick_bn(N);
+    if (bn == 0) return fail(DDC_E_INVALID, "N=%d must be a multiple of 16", N);
+    const uint64_t Mp = (static_cast<uint64_t>(M) + GEMM_BM - 1) / GEMM_BM * GEMM_BM;
+    CUtensorMap tmA, tmB;
+    TRY(make_tmap(&tmB, W, N, K, bn));
+    GemmParams p{};
+    p.M = M; p.N = N; p.K = K; p.bn = bn; p.stages = pick_stages(K, bn); p.ln_eps = 1e-5f;
+    p.bias = bias;
+    if (epi == EPI_BF16 || epi == EPI_BF16_GELU) { p.out_bf16 = static_cast<bf16*>(out); p.ld_bf16 = ld_out; }
+    else { p.out_f32 = static_cast<float*>(out); p.ld_f32 = ld_out; }
+    if (amode == A_LN) {
+        if (ln_g == nullptr || ln_b == nullptr) return fail(DDC_E_INVALID, "LayerNorm parameters are NULL");
+        p.x = static_cast<const float*>(A); p.ldx = K; p.ln_g = ln_g; p.ln_b = ln_b;
+        tmA = tmB;
+        switch (epi) {
+            case EPI_BF16: return launch_gemm<A_LN, EPI_BF16>(tmA, tmB, p, st);
+            case EPI_BF16_GELU: return launch_gemm<A_LN, EPI_BF16_GELU>(tmA, tmB, p, st);
+            case EPI_RESID: return launch_gemm<A_LN, EPI_RESID>(tmA, tmB, p, st);
+            case EPI_F32: return launch_gemm<A_LN, EPI_F32>(tmA, tmB, p, st);
+        }
+    } else if (amode == A_TMA) {
+        TRY(make_tmap(&tmA, A, Mp, K, GEMM_BM));
+        switch (epi) {
+            case EPI_BF16: return launch_gemm<A_TMA, EPI_BF16>(tmA, tmB, p, st);
+            case EPI_BF16_GELU: return launch_gemm<A_TMA, EPI_BF16_GELU>(tmA, tmB, p, st);
+            case EPI_RESID: return launch_gemm<A_TMA, EPI_RESID>(tmA, tmB, p, st);
+            case EPI_F32: return launch_gemm<A_TMA, EPI_F32>(tmA, tmB, p, st);
+        }
+    }
+    return fail(DDC_E_INVALID, "amode=%d epi=%d", amode, epi);
+}
+
+extern "C" int ddc_k_attention(const void* qkv, void* out, int32_t batch, int32_t L, int32_t C, int32_t heads,
+                               void* stream) {
+    if (qkv == nullptr || out == nullptr || batch <= 0 || L <= 0) return fail(DDC_E_INVALID, "bad argument");
+    return run_attention(static_cast<const bf16*>(qkv), static_cast<bf16*>(out), batch, L, C, heads,
+                         static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ddc_k_patchify(const float* x, void* ap, int32_t batch, int32_t H, int32_t W, int32_t patch, int32_t Kp,
+                              void* stream) {
+    if (x == nullptr || ap == nullptr || batch <= 0 || patch <= 0 || patch % 2 || H % patch || W % patch ||
+        Kp < 3 * patch * patch || Kp % 2)
+        return fail(DDC_E_INVALID, "bad argument");
+    const int L = (H / patch) * (W / patch) + 1;
+    patchify_kernel<<<dim3(H / patch, batch), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        x, static_cast<bf16*>(ap), H, W, patch, L, Kp, nullptr);
+    CK(cudaGetLastError());
+    return DDC_OK;
+}
+
+extern "C" int ddc_k_head_ddim(const float* y, int32_t ldy, float* x, int32_t batch, int32_t H, int32_t W, int32_t patch,
+                               const ddc_step* host_step, float* x0_out, float* eps_out, void* stream) {
+    if (y == nullptr || x == nullptr || host_step == nullptr || batch <= 0 || patch <= 0 || H % patch || W % patch)
+        return fail(DDC_E_INVALID, "bad argument");
+    HeadDdimParams q{};
+    q.y = y; q.ldy = ldy; q.x = x; q.H = H; q.W = W; q.p = patch; q.L = (H / patch) * (W / patch) + 1; q.B = batch;
+    q.tbl = nullptr; q.cur = nullptr;
+    memcpy(&q.one, host_step, sizeof(StepEntry));
+    q.one.flags |= 1;
+    q.x0_last = x0_out; q.x0_seq = nullptr; q.eps_seq = eps_out;
+    const size_t smem = static_cast<size_t>(W / patch) * (3 * patch * patch + 1) * sizeof(float);
+    head_ddim_kernel<MODE_STEP><<<dim3(H / patch, batch), 256, smem, static_cast<cudaStream_t>(stream)>>>(q);
+    CK(cudaGetLastError());
+    return DDC_OK;
+}

@@ -1,0 +1,327 @@
+"""Drop-in ``DiffusionVisionTransformer`` whose arithmetic runs in the sm_100a CUDA library.
+
+Mirrors the public surface of the reference class (ViT.py:158-256 and the extra cold-diffusion
+methods of ViT_draft2drawing.py:259-309): same constructor keywords, same parameter names and
+shapes (so a reference checkpoint loads with ``strict=True`` and ``state_dict()`` round-trips),
+same ``forward / sampler / diffusion_sequence / cold_sampler / cold_diffusion_sequence``
+signatures, return types and error behaviour.  The ``nn`` sub-modules below are parameter
+containers only -- their ``forward`` is never called; every tensor op happens behind
+``include/ddimcold.h``.  There is no eager-PyTorch fallback: without the built library or
+without a B200 the compute methods raise.
+
+Deliberate differences from the reference, all documented in DESIGN.md:
+  * eval semantics only (Dropout / DropPath are identity; the reference's own ``main()``
+    forgot ``.eval()``);
+  * a bad ``k`` raises the reference's ``ValueError: math domain error`` *before* any GPU work
+    instead of mid-loop;
+  * the per-step progress print (ViT.py:235) is emitted once, after the loop;
+  * optional ``noise=`` / ``draft2drawing`` extensions.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import time
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+class _PatchEmbed(nn.Module):
+    """Parameter holder for the stride-p conv (reference ViT.py:141-150)."""
+
+    def __init__(self, img_size, patch_size, in_chans, embed_dim):
+        super().__init__()
+        self.num_patches = (img_size[0] // patch_size) * (img_size[1] // patch_size)
+        self.img_size = img_size
+        self.patch_size = patch_size
+        self.proj = nn.Conv2d(in_chans, embed_dim, kernel_size=patch_size, stride=patch_size)
+
+
+class _Attn(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.qkv = nn.Linear(dim, dim * 3, bias=True)
+        self.proj = nn.Linear(dim, dim)
+
+
+class _Mlp(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.fc1 = nn.Linear(dim, dim)
+        self.fc2 = nn.Linear(dim, dim)
+
+
+class _Block(nn.Module):
+    """Parameter holder with the reference's names (ViT.py:120-130)."""
+
+    def __init__(self, dim):
+        super().__init__()
+        self.norm1 = nn.LayerNorm(dim)
+        self.attn = _Attn(dim)
+        self.norm2 = nn.LayerNorm(dim)
+        self.mlp = _Mlp(dim)
+
+
+class _DevicePlan:
+    """Arenas + C plan for one (device, max_batch)."""
+
+    def __init__(self, shape: _lib.Shape, max_batch: int, device: torch.device):
+        lib = _lib.load()
+        self.max_batch = max_batch
+        self.device = device
+        wb, kb = C.c_size_t(0), C.c_size_t(0)
+        _lib.check(lib.ddc_arena_bytes(C.byref(shape), max_batch, C.byref(wb), C.byref(kb)))
+        self.weights = torch.zeros(wb.value, dtype=torch.uint8, device=device)
+        self.work = torch.zeros(kb.value, dtype=torch.uint8, device=device)
+        torch.cuda.synchronize(device)
+        handle = C.c_void_p()
+        _lib.check(lib.ddc_plan_create(C.byref(shape), max_batch, device.index, self.weights.data_ptr(), wb.value,
+                                       self.work.data_ptr(), kb.value, C.byref(handle)))
+        self.handle = handle
+        self.packed_key = None
+        self.stream = torch.cuda.Stream(device=device)
+
+    def close(self):
+        if self.handle:
+            _lib.load().ddc_plan_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DiffusionVisionTransformer(nn.Module):
+    """ Vision Transformer x0-predictor + DDIM / cold samplers, B200-native. """
+
+    #: images per library call; larger N is processed in chunks of this size
+    max_batch_per_call = 1024
+
+    def __init__(self, img_size=[64, 64], patch_size=8, in_chans=3, embed_dim=256, depth=3,
+                 num_heads=4, mlp_ratio=1., qkv_bias=True, qk_scale=None, drop_rate=0.1, attn_drop_rate=0.1,
+                 drop_path_rate=0.1, norm_layer=nn.LayerNorm, emb=None, total_steps=2000, **kwargs):
+        super().__init__()
+        if mlp_ratio != 1.0:
+            raise NotImplementedError("only mlp_ratio=1.0 is built (every reference constructor call uses it)")
+        if not qkv_bias or qk_scale is not None or norm_layer is not nn.LayerNorm:
+            raise NotImplementedError("only qkv_bias=True, qk_scale=None, norm_layer=nn.LayerNorm are built")
+        self.num_features = self.embed_dim = embed_dim
+        self.patch_size = patch_size
+        self.in_chans = in_chans
+        self.img_size = img_size
+        self.total_steps = total_steps
+        self.num_heads = num_heads
+        self.depth = depth
+        # construction and init order follow the reference so that one torch seed yields the
+        # same random-init weights in both classes (ViT.py:169-196)
+        self.patch_embed = _PatchEmbed(img_size, patch_size, in_chans, embed_dim)
+        num_patches = self.patch_embed.num_patches
+        self.cls_token = nn.Parameter(torch.zeros(1, 1, embed_dim))
+        self.time_embed = nn.Embedding(total_steps, embed_dim)
+        self.pos_embed = nn.Parameter(torch.zeros(1, num_patches + 1, embed_dim))
+        self.blocks = nn.ModuleList([_Block(embed_dim) for _ in range(depth)])
+        self.norm = nn.LayerNorm(embed_dim)
+        self.head = nn.Linear(embed_dim, in_chans * patch_size ** 2)
+        nn.init.trunc_normal_(self.pos_embed, std=.02)
+        nn.init.trunc_normal_(self.cls_token, std=.02)
+        nn.init.trunc_normal_(self.time_embed.weight, std=.02)
+        for m in self.modules():
+            if isinstance(m, nn.Linear):
+                nn.init.trunc_normal_(m.weight, std=.02)
+                nn.init.constant_(m.bias, 0)
+            elif isinstance(m, nn.LayerNorm):
+                nn.init.constant_(m.bias, 0)
+                nn.init.constant_(m.weight, 1.0)
+        self._plans: dict = {}
+        self.last_timing = {}
+
+    # ------------------------------------------------------------------ plumbing
+    def _shape(self) -> _lib.Shape:
+        return _lib.Shape(self.img_size[0], self.img_size[1], self.patch_size, self.embed_dim, self.depth,
+                          self.num_heads, self.in_chans, self.total_steps)
+
+    def _ordered_params(self):
+        return [p for _, p in self.state_dict(keep_vars=True).items()]
+
+    def _plan(self, device, batch: int) -> _DevicePlan:
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise RuntimeError("ddim_cold_b200 computes on CUDA (sm_100a) only; there is no CPU path. "
+                               f"Got device={device}.")
+        if device.index is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        if self.cls_token.device != device:
+            raise RuntimeError(f"model parameters live on {self.cls_token.device}, sampler asked for {device}: "
+                               "call model.to(device) first (the reference requires the same, ViT.py:281)")
+        plan = self._plans.get(device)
+        if plan is None or plan.max_batch < batch:
+            if plan is not None:
+                torch.cuda.synchronize(device)
+                plan.close()
+            cap = max(batch, min(self.max_batch_per_call, 1 << max(0, (batch - 1).bit_length())))
+            plan = _DevicePlan(self._shape(), cap, device)
+            self._plans[device] = plan
+        params = self._ordered_params()
+        key = tuple((p.data_ptr(), p._version) for p in params)
+        if plan.packed_key != key:
+            keep = []
+            ptrs = (C.c_void_p * len(params))()
+            for i, p in enumerate(params):
+                q = p.detach()
+                if q.dtype != torch.float32 or not q.is_contiguous():
+                    q = q.float().contiguous()
+                    keep.append(q)
+                ptrs[i] = q.data_ptr()
+            cur = torch.cuda.current_stream(device)
+            _lib.check(_lib.load().ddc_pack_weights(plan.handle, ptrs, len(params), cur.cuda_stream))
+            cur.synchronize()
+            plan.packed_key = key
+        return plan
+
+    # ------------------------------------------------------------------ forward
+    @torch.no_grad()
+    def forward(self, x, t):
+        """x0 prediction for x [B,3,H,W] at per-sample timesteps t [B] (reference ViT.py:208-218)."""
+        if x.dim() != 4 or tuple(x.shape[1:]) != (self.in_chans, self.img_size[0], self.img_size[1]):
+            raise RuntimeError(f"expected x of shape [B,{self.in_chans},{self.img_size[0]},{self.img_size[1]}], "
+                               f"got {tuple(x.shape)}")
+        B = x.shape[0]
+        if t.numel() != B:
+            raise RuntimeError(f"t must have {B} elements, got {t.numel()}")
+        t_host_ok = t.to(torch.int64)
+        if bool(((t_host_ok < 0) | (t_host_ok >= self.total_steps)).any()):
+            raise IndexError("index out of range in self")          # nn.Embedding's error (ViT.py:204)
+        out = torch.empty_like(x, dtype=torch.float32)
+        xs = x.detach().float().contiguous()
+        ts = t.to(device=x.device, dtype=torch.int32).contiguous()
+        lib = _lib.load()
+        cap = self.max_batch_per_call
+        for b0 in range(0, B, cap):
+            b1 = min(B, b0 + cap)
+            plan = self._plan(x.device, b1 - b0)
+            st = torch.cuda.current_stream(x.device).cuda_stream
+            _lib.check(lib.ddc_forward(plan.handle, xs[b0:b1].data_ptr(), ts[b0:b1].data_ptr(), b1 - b0,
+                                       out[b0:b1].data_ptr(), st))
+        return out
+
+    # ------------------------------------------------------------------ loops
+    def _run_loop(self, device, x_init_cpu: torch.Tensor, table, n_steps: int, want_seq: bool = False,
+                  want_eps: bool = False, use_graph: bool = True):
+        """Run the table-driven loop on `device` for CPU initial states [N,3,H,W].
+        Returns (x0_last_cpu, x0_seq_cpu | None, eps_seq_cpu | None)."""
+        lib = _lib.load()
+        N = x_init_cpu.shape[0]
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("ddim_cold_b200 computes on CUDA (sm_100a) only; there is no CPU path. "
+                               f"Got device={dev}.")
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        cap = self.max_batch_per_call
+        x_pin = x_init_cpu.contiguous().float()
+        if not x_pin.is_pinned():
+            x_pin = x_pin.pin_memory()
+        out = torch.empty((N,) + tuple(x_pin.shape[1:]), dtype=torch.float32).pin_memory()
+        seq = torch.empty((n_steps, N) + tuple(x_pin.shape[1:]), dtype=torch.float32) if want_seq else None
+        eps = torch.empty((n_steps, N) + tuple(x_pin.shape[1:]), dtype=torch.float32) if want_eps else None
+        t_h2d = t_gpu = 0.0
+        for b0 in range(0, N, cap):
+            b1 = min(N, b0 + cap)
+            B = b1 - b0
+            plan = self._plan(dev, B)
+            s = plan.stream
+            s.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(s):
+                x = x_pin[b0:b1].to(dev, non_blocking=True)
+                x0 = torch.empty_like(x)
+                x0s = torch.empty((n_steps,) + tuple(x.shape), dtype=torch.float32, device=dev) if want_seq else None
+                eps_d = torch.empty((n_steps,) + tuple(x.shape), dtype=torch.float32, device=dev) if want_eps else None
+                _lib.check(lib.ddc_sample(plan.handle, x.data_ptr(), B, table, n_steps, x0.data_ptr(),
+                                          x0s.data_ptr() if want_seq else None,
+                                          eps_d.data_ptr() if want_eps else None,
+                                          1 if use_graph else 0, s.cuda_stream))
+                out[b0:b1].copy_(x0, non_blocking=True)
+                if want_seq:
+                    seq[:, b0:b1].copy_(x0s)
+                if want_eps:
+                    eps[:, b0:b1].copy_(eps_d)
+            s.synchronize()
+        return out, seq, eps
+
+    def _print_progress(self, last_t, start_time):
+        print(f"\rnoise level {last_t}  {time.time() - start_time:.2f}", end='')
+
+    @torch.no_grad()
+    def sampler(self, device, k=10, N=128, noise=None):
+        """DDIM sampling (reference ViT.py:220-237): CPU fp32 [N,3,H,W] in [0,1], the last step's
+        clamped x0 prediction.  The initial noise is drawn on the CPU from the global torch RNG
+        exactly like the reference unless `noise` ([N,3,H,W], CPU or CUDA) is given."""
+        start_time = time.time()
+        table, n = _lib.ddim_table(k, self.total_steps)
+        noisy_img = torch.normal(0, 1, (N, 3, self.img_size[0], self.img_size[1])) if noise is None \
+            else noise.detach().float().cpu()
+        x0, _, _ = self._run_loop(device, noisy_img, table, n)
+        self._print_progress(table[n - 1].t, start_time)
+        return (x0 + 1) / 2
+
+    @torch.no_grad()
+    def diffusion_sequence(self, device, k=100, N=5, noise=None):
+        """reference ViT.py:239-256: [(x_T+1)/2] followed by every step's (x0+1)/2, all on CPU."""
+        start_time = time.time()
+        table, n = _lib.ddim_table(k, self.total_steps)
+        noisy_img = torch.normal(0, 1, (N, 3, self.img_size[0], self.img_size[1])) if noise is None \
+            else noise.detach().float().cpu()
+        _, seq, _ = self._run_loop(device, noisy_img, table, n, want_seq=True)
+        self._print_progress(table[n - 1].t, start_time)
+        return [(noisy_img + 1) / 2] + [(seq[i] + 1) / 2 for i in range(n)]
+
+    def _cold_init(self, N, z=None):
+        z = torch.normal(0, 1, (N, 3)) if z is None else z.detach().float().cpu()
+        return z.unsqueeze(2).unsqueeze(3).expand(-1, -1, self.img_size[0], self.img_size[1]).contiguous()
+
+    @torch.no_grad()
+    def cold_sampler(self, device, k=10, N=49, z=None):
+        """Cold-diffusion sampling, t = 6..1 (reference ViT_draft2drawing.py:259-288; k is unused
+        there as well)."""
+        start_time = time.time()
+        table, n = _lib.cold_table()
+        x0, _, _ = self._run_loop(device, self._cold_init(N, z), table, n)
+        self._print_progress(1, start_time)
+        return (x0 + 1) / 2
+
+    @torch.no_grad()
+    def cold_diffusion_sequence(self, device, N=5, z=None):
+        """reference ViT_draft2drawing.py:290-309."""
+        start_time = time.time()
+        table, n = _lib.cold_table()
+        x_init = self._cold_init(N, z)
+        _, seq, _ = self._run_loop(device, x_init, table, n, want_seq=True)
+        self._print_progress(1, start_time)
+        return [(x_init + 1) / 2] + [(seq[i] + 1) / 2 for i in range(n)]
+
+    @torch.no_grad()
+    def draft2drawing(self, device, draft, t_start, k=10, N=1, noise=None):
+        """Batched form of the draft->drawing script loop (reference ViT_draft2drawing.py:391-409):
+        x = N(0,1)*sqrt(1-a) + draft*sqrt(a), a = 1-sqrt(t_start/T); DDIM from t_start.
+        draft: [3,H,W] or [N,3,H,W] in [-1,1].  Returns CPU (x0+1)/2."""
+        table, n = _lib.ddim_table(k, self.total_steps, t_start)
+        alpha = 1 - math.sqrt(t_start / self.total_steps)
+        z = torch.normal(0, 1, (N, 3, self.img_size[0], self.img_size[1])) if noise is None \
+            else noise.detach().float().cpu()
+        x = z * math.sqrt(1 - alpha) + draft.detach().float().cpu() * math.sqrt(alpha)
+        x0, _, _ = self._run_loop(device, x, table, n)
+        return (x0 + 1) / 2
+
+    @torch.no_grad()
+    def denoise_trace(self, device, x_init, k=10, t_start=None, use_graph=True):
+        """Parity tap (no reference counterpart): runs the loop and returns per-step clamped x0
+        and derived eps (ViT.py:229,233) as CPU tensors [steps,N,3,H,W], plus the last x0."""
+        table, n = _lib.ddim_table(k, self.total_steps, t_start)
+        x0, seq, eps = self._run_loop(device, x_init.detach().float().cpu(), table, n, want_seq=True,
+                                      want_eps=True, use_graph=use_graph)
+        return x0, seq, eps

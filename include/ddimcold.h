@@ -1,0 +1,137 @@
+/* ddimcold.h -- C ABI of the B200 (sm_100a) DDIM sampling path of DDIM-COLD.
+ *
+ * The reference has no FFI: the path sits behind a Python class,
+ * DiffusionVisionTransformer (reference ViT.py:158-256, ViT_draft2drawing.py:158-329).
+ * This header is the boundary a host binds instead of that class's tensor arithmetic; the
+ * Python drop-in in ddim_cold_b200/vit.py binds it with ctypes.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative DDC_E_* code otherwise, and never
+ *     throws; ddc_last_error() returns a thread-local description of the last failure;
+ *   - all tensor pointers are DEVICE pointers unless the name says host;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream);
+ *   - the library performs no device allocation: the caller owns the weight arena and the
+ *     work arena (sizes from ddc_arena_bytes) and passes them to ddc_plan_create;
+ *   - a plan is bound to one device, one shape and a maximum batch; plans are independent,
+ *     so one process can drive eight GPUs with eight plans, or eight processes one each.
+ */
+#ifndef DDIMCOLD_H_
+#define DDIMCOLD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDC_OK 0
+#define DDC_E_INVALID (-1)    /* bad argument / unsupported shape */
+#define DDC_E_CUDA (-2)       /* a CUDA runtime or driver call failed */
+#define DDC_E_DOMAIN (-3)     /* schedule undefined for this k (reference: math domain error) */
+#define DDC_E_STATE (-4)      /* weights not packed, arena too small, ... */
+
+/* Constructor arguments that fix every tensor shape (reference ViT.py:160-162). */
+typedef struct ddc_shape {
+    int32_t img_h, img_w;   /* img_size */
+    int32_t patch;          /* patch_size (even) */
+    int32_t embed;          /* embed_dim, multiple of 64, <= 512 */
+    int32_t depth;
+    int32_t heads;          /* num_heads; embed/heads must be 32 or 64 */
+    int32_t in_chans;       /* 3 */
+    int32_t total_steps;    /* rows of time_embed (2000) */
+} ddc_shape;
+
+/* One entry of the per-step table (mirrors the device struct).  x' = a*x + b*x0 is the
+ * collapsed form of reference ViT.py:233-234; eps = (x - sqrt_at*x0) * inv_sqrt_1mat is
+ * ViT.py:233.  flags bit0 marks the step whose x0 is the sampler's return value. */
+typedef struct ddc_step {
+    int32_t t;
+    int32_t flags;
+    float a, b, sqrt_at, inv_sqrt_1mat;
+    float pad0, pad1;
+} ddc_step;
+
+typedef struct ddc_plan ddc_plan;
+
+const char* ddc_last_error(void);
+int ddc_version(void);
+
+/* Schedule of the DDIM loop `for t in range(t_start, 0, -k)` (reference ViT.py:226,231-232;
+ * t_start = total_steps-1 for sampler(), the draft's t_start for ViT_draft2drawing.py:399).
+ * Scalars are computed in double precision exactly as the reference's math.sqrt expressions
+ * and rounded to float once.  Writes at most `capacity` entries to host memory, returns the
+ * count in *n_steps.  DDC_E_DOMAIN when some step needs sqrt of a negative number or divides
+ * by alpha_tk = 0 -- the cases where the reference raises mid-loop (ValueError: math domain
+ * error / ZeroDivisionError). */
+int ddc_ddim_table(int32_t k, int32_t total_steps, int32_t t_start, ddc_step* host_table, int32_t capacity,
+                   int32_t* n_steps);
+
+/* Cold-diffusion schedule: t = 6..1, x <- clamp(f(x, t))  (ViT_draft2drawing.py:272-288). */
+int ddc_cold_table(ddc_step* host_table, int32_t capacity, int32_t* n_steps);
+
+/* Arena sizes in bytes for `shape` at up to `max_batch` images per call. */
+int ddc_arena_bytes(const ddc_shape* shape, int32_t max_batch, size_t* weight_bytes, size_t* work_bytes);
+
+/* Create a plan over caller-owned device arenas (256-byte aligned; the work arena must be
+ * zero-filled by the caller once before first use). */
+int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_t device, void* weight_arena, size_t weight_bytes,
+                    void* work_arena, size_t work_bytes, ddc_plan** out);
+int ddc_plan_destroy(ddc_plan* plan);
+
+/* Pack an fp32 state dict into the plan's weight arena (bf16 K-major GEMM operands, folded
+ * cls/pos/conv-bias rows, fp32 time table).  `tensors` is a HOST array of `n_tensors` device
+ * pointers in the reference's state_dict order: cls_token, pos_embed, patch_embed.proj.weight,
+ * patch_embed.proj.bias, time_embed.weight, then per block norm1.{weight,bias},
+ * attn.qkv.{weight,bias}, attn.proj.{weight,bias}, norm2.{weight,bias}, mlp.fc1.{weight,bias},
+ * mlp.fc2.{weight,bias}, then norm.{weight,bias}, head.{weight,bias}
+ * (9 + 12*depth entries; reference ViT.py:169-183). */
+int ddc_pack_weights(ddc_plan* plan, const float* const* tensors, int32_t n_tensors, void* stream);
+
+/* One evaluation of the x0 predictor: out = forward(x, t), unclamped
+ * (reference ViT.py:208-218).  x, out: [B,3,H,W] fp32; t: [B] int32 on the device. */
+int ddc_forward(ddc_plan* plan, const float* x, const int32_t* t, int32_t batch, float* out, void* stream);
+
+/* The whole sampling loop (reference ViT.py:226-236): for each table entry run the predictor
+ * at entry.t, clamp to [-1,1], apply the DDIM update in place on `x`.
+ *   x        [B,3,H,W] fp32, in: x_T (or the partially noised draft), out: the final state
+ *   x0_last  [B,3,H,W] fp32, receives the clamped x0 of the flagged (last) step -- the tensor
+ *            the reference's sampler returns as (x0+1)/2; may be NULL
+ *   x0_seq   [n_steps,B,3,H,W] fp32 or NULL: every step's clamped x0 (diffusion_sequence,
+ *            ViT.py:254, and parity taps)
+ *   eps_seq  [n_steps,B,3,H,W] fp32 or NULL: every step's derived eps (ViT.py:233)
+ *   use_graph != 0 captures one step as a CUDA graph and replays it n_steps times. */
+int ddc_sample(ddc_plan* plan, float* x, int32_t batch, const ddc_step* host_table, int32_t n_steps, float* x0_last,
+               float* x0_seq, float* eps_seq, int32_t use_graph, void* stream);
+
+/* Number of kernel launches one ddc_forward / one step of ddc_sample issues. */
+int ddc_launches_per_step(const ddc_plan* plan);
+
+/* ---- kernel-level entry points (unit tests; hosts that schedule kernels themselves) ---- */
+
+/* out = epilogue(A' * W^T + bias).  amode 0: A is bf16 [m_pad, K]; amode 1: A is fp32
+ * [m_pad, K] and A' = LayerNorm(A; ln_g, ln_b, eps 1e-5) (reference ViT.py:124,128,182).
+ * epi 0: bf16 out; 1: bf16 gelu_erf out (ViT.py:85-86); 2: fp32 out += (residual, in place,
+ * ViT.py:136-137); 3: fp32 out.  W: bf16 [N, K]; K % 64 == 0; N % 16 == 0; rows of A are
+ * allocated up to a multiple of 128, only the first M rows of out are written. */
+int ddc_k_gemm(int32_t amode, int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const float* ln_g,
+               const float* ln_b, const void* W, const float* bias, void* out, int32_t ld_out, void* stream);
+
+/* softmax(q k^T / sqrt(d)) v per (image, head) (reference ViT.py:107-114).
+ * qkv: bf16 [B*L, 3C] (column s*C + head*d + e); out: bf16 [B*L, C]. */
+int ddc_k_attention(const void* qkv, void* out, int32_t batch, int32_t L, int32_t C, int32_t heads, void* stream);
+
+/* Patchify (im2col of the stride-p conv, reference ViT.py:150,154): x fp32 [B,3,H,W] ->
+ * ap bf16 [B*L, Kp] with a zero cls row per image and zero K padding. */
+int ddc_k_patchify(const float* x, void* ap, int32_t batch, int32_t H, int32_t W, int32_t patch, int32_t Kp,
+                   void* stream);
+
+/* Unpatchify + clamp + DDIM update (reference ViT.py:214-217,229,233-234) for one step given
+ * by value.  y: fp32 [B*L, ldy] head output; x updated in place; x0_out / eps_out may be NULL. */
+int ddc_k_head_ddim(const float* y, int32_t ldy, float* x, int32_t batch, int32_t H, int32_t W, int32_t patch,
+                    const ddc_step* host_step, float* x0_out, float* eps_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDIMCOLD_H_ */

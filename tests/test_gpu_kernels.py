@@ -1,0 +1,137 @@
+"""GPU: each CUDA kernel through its C-ABI entry point against a plain fp32 torch restatement
+of the same op (operands pre-rounded to bf16 where the kernel consumes bf16, so the
+tolerance only has to cover fp32 accumulation order and the bf16 rounding of the output)."""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from ddim_cold_b200 import _lib
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return _lib.load()
+
+
+def _check(code):
+    from ddim_cold_b200 import _lib
+    _lib.check(code)
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _pad_rows(t, mult=128):
+    m = t.shape[0]
+    mp = (m + mult - 1) // mult * mult
+    out = torch.zeros((mp,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+    out[:m] = t
+    return out
+
+
+GEMM_SHAPES = [(200, 128, 64), (130, 192, 384), (1000, 1152, 384), (257 * 3, 768, 256), (515, 48, 256),
+               (65 * 40, 384, 192), (128, 64, 64), (4097, 384, 384)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+@pytest.mark.parametrize("amode", [0, 1])
+@pytest.mark.parametrize("epi", [0, 1, 2, 3])
+def test_gemm(lib, M, N, K, amode, epi):
+    g = torch.Generator(device="cuda").manual_seed(M * 7 + N * 3 + K + amode * 11 + epi)
+    dev = "cuda"
+    W = (torch.randn(N, K, device=dev, generator=g) * 0.05).to(torch.bfloat16)
+    bias = torch.randn(N, device=dev, generator=g) * 0.1
+    if amode == 0:
+        A = _pad_rows(torch.randn(M, K, device=dev, generator=g).to(torch.bfloat16))
+        A_eff = A[:M].float()
+        ln_g = ln_b = None
+    else:
+        A = _pad_rows(torch.randn(M, K, device=dev, generator=g) * 1.7 + 0.3)
+        ln_g = 1 + 0.1 * torch.randn(K, device=dev, generator=g)
+        ln_b = 0.1 * torch.randn(K, device=dev, generator=g)
+        A_eff = torch.nn.functional.layer_norm(A[:M], (K,), ln_g, ln_b, 1e-5).to(torch.bfloat16).float()
+    ref = A_eff @ W.float().T + bias
+    if epi == 1:
+        ref = torch.nn.functional.gelu(ref)
+    if epi in (0, 1):
+        out = torch.full((M + 3, N), 7.0, device=dev, dtype=torch.bfloat16)
+    else:
+        out = torch.randn(M + 3, N, device=dev, generator=g)
+    before = out.clone()
+    if epi == 2:
+        ref = ref + before[:M].float()
+    _check(lib.ddc_k_gemm(amode, epi, M, N, K, A.data_ptr(), ln_g.data_ptr() if amode else None,
+                          ln_b.data_ptr() if amode else None, W.data_ptr(), bias.data_ptr(), out.data_ptr(), N,
+                          _stream()))
+    torch.cuda.synchronize()
+    got = out[:M].float()
+    tol = 2e-2 if epi in (0, 1) else 3e-3          # bf16 output rounding vs fp32 output
+    err = (got - ref).abs().max().item()
+    assert err < tol * max(1.0, ref.abs().max().item()), (err, ref.abs().max().item())
+    assert torch.equal(out[M:], before[M:]), "rows beyond M were written"
+
+
+ATT_SHAPES = [(3, 65, 384, 12), (2, 257, 256, 4), (1, 626, 384, 12), (5, 17, 64, 2), (2, 33, 128, 2), (4, 16, 64, 1)]
+
+
+@pytest.mark.parametrize("B,L,Cdim,heads", ATT_SHAPES)
+def test_attention(lib, B, L, Cdim, heads):
+    g = torch.Generator(device="cuda").manual_seed(L + heads)
+    d = Cdim // heads
+    qkv = (torch.randn(B * L, 3 * Cdim, device="cuda", generator=g) * 1.5).to(torch.bfloat16)
+    out = torch.zeros(B * L, Cdim, device="cuda", dtype=torch.bfloat16)
+    _check(lib.ddc_k_attention(qkv.data_ptr(), out.data_ptr(), B, L, Cdim, heads, _stream()))
+    torch.cuda.synchronize()
+    x = qkv.float().reshape(B, L, 3, heads, d).permute(2, 0, 3, 1, 4)
+    q, k, v = x[0], x[1], x[2]
+    p = ((q @ k.transpose(-2, -1)) * d ** -0.5).softmax(dim=-1)
+    ref = (p @ v).transpose(1, 2).reshape(B * L, Cdim)
+    err = (out.float() - ref).abs().max().item()
+    assert err < 2e-2 * max(1.0, ref.abs().max().item()), err
+
+
+@pytest.mark.parametrize("B,H,W,p", [(3, 64, 64, 8), (2, 64, 64, 4), (1, 200, 200, 8), (2, 16, 16, 4), (2, 32, 48, 4)])
+def test_patchify(lib, B, H, W, p):
+    x = torch.randn(B, 3, H, W, device="cuda")
+    P = 3 * p * p
+    Kp = (P + 63) // 64 * 64
+    n = (H // p) * (W // p)
+    L = n + 1
+    ap = torch.full((B * L, Kp), 9.0, device="cuda", dtype=torch.bfloat16)
+    _check(lib.ddc_k_patchify(x.data_ptr(), ap.data_ptr(), B, H, W, p, Kp, _stream()))
+    torch.cuda.synchronize()
+    ref = x.reshape(B, 3, H // p, p, W // p, p).permute(0, 2, 4, 1, 3, 5).reshape(B, n, P).to(torch.bfloat16)
+    got = ap.reshape(B, L, Kp)
+    assert torch.equal(got[:, 1:, :P], ref)
+    assert torch.count_nonzero(got[:, 0]) == 0 and torch.count_nonzero(got[:, :, P:]) == 0
+
+
+@pytest.mark.parametrize("B,H,W,p", [(3, 64, 64, 8), (2, 64, 64, 4), (1, 200, 200, 8), (2, 16, 16, 4)])
+@pytest.mark.parametrize("t,k", [(1999, 20), (999, 20), (19, 20), (1, 1)])
+def test_head_ddim(lib, B, H, W, p, t, k):
+    from ddim_cold_b200 import _lib
+    from oracle import ddim_oracle as O
+    sh = O.Shape(H, W, p, 64, 1, 2)
+    P = 3 * p * p
+    L = sh.tokens
+    y = torch.randn(B * L, P, device="cuda") * 0.8
+    x = torch.randn(B, 3, H, W, device="cuda")
+    x_before = x.clone()
+    x0 = torch.empty_like(x)
+    eps = torch.empty_like(x)
+    tab, n = _lib.ddim_table(k, 2000, t)
+    _check(lib.ddc_k_head_ddim(y.data_ptr(), P, x.data_ptr(), B, H, W, p, C.byref(tab[0]), x0.data_ptr(),
+                               eps.data_ptr(), _stream()))
+    torch.cuda.synchronize()
+    y_np = y.cpu().numpy().reshape(B, L, P)
+    x0_ref = np.clip(O.unpatchify(y_np[:, 1:], sh), -1, 1)
+    eps_ref, xn_ref = O.ddim_update(x_before.cpu().numpy().astype(np.float64), x0_ref.astype(np.float64), t, k)
+    assert np.array_equal(x0.cpu().numpy(), x0_ref)                      # pure data movement + clamp: bit exact
+    assert np.abs(x.cpu().numpy() - xn_ref).max() < 1e-5 * max(1.0, np.abs(xn_ref).max())
+    assert np.abs(eps.cpu().numpy() - eps_ref).max() < 1e-5 * max(1.0, np.abs(eps_ref).max())

@@ -1,0 +1,171 @@
+"""GPU: the drop-in class (through the C ABI) against the CPU oracle and the fixtures recorded
+from the unmodified reference.
+
+Tolerances (north_star): teacher-forced per-step eps within 1e-2 max-abs in bf16; final images
+within a PSNR bound.  The CUDA path computes GEMM operands in bf16 with fp32 accumulation, fp32
+LayerNorm / softmax statistics and an fp32 residual stream and image state.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+EPS_TOL = 1e-2          # north_star: per-step eps, bf16 mode, max-abs, teacher-forced
+X0_TOL = 1e-2
+PSNR_MIN = 40.0         # final images in [0,1] vs the fp32 reference sampler, free-running
+
+
+def psnr(a, b):
+    mse = float(np.mean((np.asarray(a, np.float64) - np.asarray(b, np.float64)) ** 2))
+    return 99.0 if mse == 0 else 10 * math.log10(1.0 / mse)
+
+
+def build(sh, sd, dev="cuda"):
+    from ddim_cold_b200 import DiffusionVisionTransformer
+    m = DiffusionVisionTransformer(img_size=[sh.img_h, sh.img_w], patch_size=sh.patch, embed_dim=sh.embed,
+                                   depth=sh.depth, num_heads=sh.heads, total_steps=sh.total_steps)
+    m.load_state_dict({k: torch.from_numpy(v.copy()) for k, v in sd.items()}, strict=True)
+    return m.eval().to(dev)
+
+
+@pytest.fixture(scope="module")
+def tiny(golden):
+    from oracle import ddim_oracle as O
+    sd = O.synth_state_dict(O.TINY, seed=11, rich=True, gain=4.0)
+    return golden("tiny"), sd, build(O.TINY, sd)
+
+
+def test_forward_tiny_vs_reference_fixture(tiny):
+    g, sd, m = tiny
+    y = m(torch.from_numpy(g["fwd_x"]).cuda(), torch.from_numpy(g["fwd_t"]).cuda()).cpu().numpy()
+    assert np.abs(y - g["fwd_y"]).max() < 2e-2
+
+
+def test_forward_rejects_bad_t(tiny):
+    _, _, m = tiny
+    with pytest.raises(IndexError):
+        m(torch.zeros(1, 3, 16, 16).cuda(), torch.tensor([2000]).cuda())
+
+
+@pytest.mark.parametrize("k", [100, 500, 2000])
+def test_sampler_tiny_vs_reference_fixture(tiny, k, capsys):
+    g, sd, m = tiny
+    img = m.sampler("cuda", k, 3, noise=torch.from_numpy(g[f"samp{k}_xT"]))
+    assert img.device.type == "cpu" and img.dtype == torch.float32 and tuple(img.shape) == (3, 3, 16, 16)
+    assert float(img.min()) >= 0.0 and float(img.max()) <= 1.0
+    assert psnr(img.numpy(), g[f"samp{k}_img"]) > PSNR_MIN
+    assert "noise level" in capsys.readouterr().out
+
+
+def test_sampler_seed_compat_with_reference(tiny):
+    """Without noise= the sampler must consume the global CPU RNG like ViT.py:224."""
+    g, sd, m = tiny
+    torch.manual_seed(123)
+    img = m.sampler("cuda", 100, 3)
+    assert psnr(img.numpy(), g["samp100_img"]) > PSNR_MIN
+
+
+def test_trace_teacher_forced_tiny(tiny):
+    g, sd, m = tiny
+    xs = torch.from_numpy(g["trace100_x_t"])          # [20, 3, 3, 16, 16]
+    for j, t in enumerate(range(1999, 0, -100)):
+        x0 = torch.clamp(m(xs[j].cuda(), torch.full((3,), t).cuda()), -1, 1).cpu().numpy()
+        assert np.abs(x0 - g["trace100_x0"][j]).max() < X0_TOL, (j, t)
+
+
+def test_bad_k_raises_before_gpu_work(tiny):
+    _, _, m = tiny
+    for k in (3, 7, 30, 4000):
+        with pytest.raises(ValueError, match="math domain error"):
+            m.sampler("cuda", k, 1)
+
+
+def test_graph_equals_direct_launch(tiny):
+    g, sd, m = tiny
+    x = torch.from_numpy(g["samp100_xT"])
+    a = m.denoise_trace("cuda", x, k=100, use_graph=True)
+    b = m.denoise_trace("cuda", x, k=100, use_graph=False)
+    for u, v in zip(a, b):
+        assert torch.equal(u, v)
+
+
+def test_deterministic_and_batch_invariant(tiny):
+    """Same sample alone or inside a batch, run twice: bit-identical (sharding must not change
+    any sample)."""
+    g, sd, m = tiny
+    x = torch.from_numpy(g["samp100_xT"])
+    a = m.sampler("cuda", 100, 3, noise=x)
+    b = m.sampler("cuda", 100, 3, noise=x)
+    c = m.sampler("cuda", 100, 1, noise=x[1:2])
+    assert torch.equal(a, b) and torch.equal(a[1:2], c)
+
+
+def test_sequence_cold_d2d_tiny(tiny):
+    from oracle import ddim_oracle as O
+    g, sd, m = tiny
+    seq = m.diffusion_sequence("cuda", 400, 2, noise=torch.from_numpy(g["seq400_xT"]))
+    assert len(seq) == 1 + 5 and np.array_equal(seq[0].numpy(), g["seq400_imgs"][0])
+    assert min(psnr(s.numpy(), r) for s, r in zip(seq, g["seq400_imgs"])) > PSNR_MIN
+    z = torch.from_numpy(g["cold_z"])
+    assert psnr(m.cold_sampler("cuda", 10, 4, z=z).numpy(), g["cold_img"]) > PSNR_MIN
+    cs = m.cold_diffusion_sequence("cuda", 4, z=z)
+    assert len(cs) == 7 and min(psnr(s.numpy(), r) for s, r in zip(cs, g["cold_seq"])) > PSNR_MIN
+    noise = torch.from_numpy(O.synth_noise((2, 3, 16, 16), seed=int(g["d2d_noise_seed"])))
+    draft = torch.from_numpy(O.synth_draft(O.TINY))
+    for t0 in (1599, 1999):
+        img = m.draft2drawing("cuda", draft, t0, k=10, N=2, noise=noise)
+        assert psnr(img.numpy(), g[f"d2d{t0}_img"]) > PSNR_MIN
+
+
+@pytest.mark.parametrize("tag,seed", [("s1", 0), ("s2", 1)])
+def test_real_shapes_teacher_forced_eps(golden, tag, seed):
+    """S1 (yaml model) and S2 (OxfordFlower.pkl shape): per-step x0 and derived eps against the
+    reference's own values at the recorded x_t, plus the free-running sampler image."""
+    from oracle import ddim_oracle as O
+    sh = {"s1": O.S1, "s2": O.S2}[tag]
+    g = golden(tag)
+    sd = O.synth_state_dict(sh, seed=seed, rich=True)
+    m = build(sh, sd)
+    worst_x0 = worst_eps = 0.0
+    for j, t in enumerate(g["tap_t"]):
+        x_t = g["tap_x_t"][j]
+        x0 = torch.clamp(m(torch.from_numpy(x_t).cuda(), torch.tensor([int(t)]).cuda()), -1, 1).cpu().numpy()
+        eps, _ = O.ddim_update(x_t, x0, int(t), 100)
+        worst_x0 = max(worst_x0, float(np.abs(x0 - g["tap_x0"][j]).max()))
+        worst_eps = max(worst_eps, float(np.abs(eps - g["tap_eps"][j]).max()))
+    print(f"{tag}: teacher-forced max|x0 err|={worst_x0:.3e} max|eps err|={worst_eps:.3e}")
+    assert worst_x0 < X0_TOL and worst_eps < EPS_TOL, (worst_x0, worst_eps)
+    img = m.sampler("cuda", 100, 2, noise=torch.from_numpy(g["xT"])).numpy()
+    p = psnr(img, g["samp100_img"])
+    print(f"{tag}: free-running sampler k=100 PSNR vs reference = {p:.1f} dB")
+    assert p > PSNR_MIN
+
+
+def test_s1_k20_eps_vs_oracle_all_steps():
+    """Config #2 schedule (k=20, 100 steps) on S1, N=2: device-side eps taps of the free-running
+    loop against the oracle evaluated at the device's own x_t (teacher-forced on the CUDA
+    trajectory), every step."""
+    from oracle import ddim_oracle as O
+    from oracle import ddim_oracle_torch as OT
+    sh = O.S1
+    sd = O.synth_state_dict(sh, seed=0, rich=True)
+    m = build(sh, sd)
+    x_T = torch.from_numpy(O.synth_noise((2, 3, 64, 64), seed=123))
+    x0_last, seq, eps = m.denoise_trace("cuda", x_T, k=20)
+    # rebuild the device trajectory x_t from its own taps: x_{t-k} = a*x_t + b*x0
+    sdt = OT.to_torch_sd(sd)
+    x = x_T.clone()
+    worst = 0.0
+    for j, t in enumerate(range(1999, 0, -20)):
+        x0_ref = torch.clamp(OT.forward(sdt, sh, x, torch.full((2,), t)), -1, 1)
+        a_t = 1 - math.sqrt((t + 1) / 2000) + 1e-5
+        eps_ref = (x - math.sqrt(a_t) * x0_ref) / math.sqrt(1 - a_t)
+        worst = max(worst, float((eps[j] - eps_ref).abs().max()))
+        a, b, _, _ = O.ddim_ab(t, 20)
+        x = (a * x.double() + b * seq[j].double()).float()
+    print(f"s1 k=20: worst teacher-forced eps error over 100 steps = {worst:.3e}")
+    assert worst < EPS_TOL
+    assert torch.equal(x0_last, seq[-1])
