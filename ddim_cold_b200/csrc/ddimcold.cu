@@ -388,15 +388,50 @@ extern "C" int ddc_pack_weights(ddc_plan* pl, const float* const* t, int32_t n_t
     return DDC_OK;
 }
 
+// ------------------------------------------------------------------------------- per-class timing
+enum { KC_PATCHIFY = 0, KC_EMBED, KC_QKV, KC_ATTN, KC_PROJ, KC_FC1, KC_FC2, KC_HEAD, KC_DDIM, KC_COUNT };
+
+struct Prof {
+    cudaStream_t st;
+    std::vector<cudaEvent_t> ev;
+    std::vector<int> cls;
+    int begin() {
+        cudaEvent_t e;
+        CK(cudaEventCreate(&e));
+        ev.push_back(e);
+        CK(cudaEventRecord(e, st));
+        return DDC_OK;
+    }
+    int mark(int c) {
+        cudaEvent_t e;
+        CK(cudaEventCreate(&e));
+        ev.push_back(e);
+        cls.push_back(c);
+        CK(cudaEventRecord(e, st));
+        return DDC_OK;
+    }
+    void release() {
+        for (cudaEvent_t e : ev) cudaEventDestroy(e);
+        ev.clear();
+        cls.clear();
+    }
+};
+#define MARK(c)                          \
+    do {                                 \
+        if (prof) TRY(prof->mark(c));    \
+    } while (0)
+
 // ------------------------------------------------------------------------------- one predictor evaluation
 // Enqueues: patchify -> embed GEMM -> depth x [LN1+qkv GEMM, attention, proj GEMM(+res),
 // LN2+fc1 GEMM(+GELU), fc2 GEMM(+res)] -> LN+head GEMM.  Leaves the head output in pl->Y.
-static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_img, bool use_step_ctr, cudaStream_t st) {
+static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_img, bool use_step_ctr, cudaStream_t st,
+                             Prof* prof = nullptr) {
     const ddc_shape& s = pl->sh;
     const int C = pl->C, L = pl->L, M = B * L;
     patchify_kernel<<<dim3(s.img_h / s.patch, B), 256, 0, st>>>(x, pl->Ap, s.img_h, s.img_w, s.patch, L, pl->Kp,
                                                                   use_step_ctr ? pl->ctr : nullptr);
     CK(cudaGetLastError());
+    MARK(KC_PATCHIFY);
     GemmParams g{};
     g.M = M;
     g.ln_eps = 1e-5f;
@@ -405,6 +440,7 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     g.out_f32 = pl->X; g.ld_f32 = C;
     g.posb = pl->posb; g.L = L; g.time_tab = pl->time_tab; g.t_img = t_img; g.tbl = pl->tbl; g.cur = pl->ctr;
     TRY((launch_gemm<A_TMA, EPI_EMBED>(pl->tm_Ap, pl->tm_wpatch, g, st)));
+    MARK(KC_EMBED);
     for (int i = 0; i < s.depth; ++i) {
         LayerW& l = pl->layers[i];
         GemmParams q{};
@@ -413,24 +449,30 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
         q.x = pl->X; q.ldx = C; q.ln_g = l.ln1_g; q.ln_b = l.ln1_b;
         q.bias = l.b_qkv; q.out_bf16 = pl->QKV; q.ld_bf16 = 3 * C;
         TRY((launch_gemm<A_LN, EPI_BF16>(l.tm_qkv, l.tm_qkv, q, st)));
+        MARK(KC_QKV);
         TRY(run_attention(pl->QKV, pl->O, B, L, C, s.heads, st));
+        MARK(KC_ATTN);
         GemmParams r{};
         r.M = M; r.N = C; r.K = C; r.bn = pl->bn_c; r.stages = pick_stages(r.K, r.bn);
         r.bias = l.b_proj; r.out_f32 = pl->X; r.ld_f32 = C;
         TRY((launch_gemm<A_TMA, EPI_RESID>(pl->tm_O, l.tm_proj, r, st)));
+        MARK(KC_PROJ);
         GemmParams f{};
         f.M = M; f.ln_eps = 1e-5f; f.N = C; f.K = C; f.bn = pl->bn_c; f.stages = pick_stages(f.K, f.bn);
         f.x = pl->X; f.ldx = C; f.ln_g = l.ln2_g; f.ln_b = l.ln2_b;
         f.bias = l.b_fc1; f.out_bf16 = pl->Hd; f.ld_bf16 = C;
         TRY((launch_gemm<A_LN, EPI_BF16_GELU>(l.tm_fc1, l.tm_fc1, f, st)));
+        MARK(KC_FC1);
         r.bias = l.b_fc2;
         TRY((launch_gemm<A_TMA, EPI_RESID>(pl->tm_Hd, l.tm_fc2, r, st)));
+        MARK(KC_FC2);
     }
     GemmParams h{};
     h.M = M; h.ln_eps = 1e-5f; h.N = pl->P; h.K = C; h.bn = pl->bn_head; h.stages = pick_stages(h.K, h.bn);
     h.x = pl->X; h.ldx = C; h.ln_g = pl->lnf_g; h.ln_b = pl->lnf_b;
     h.bias = pl->b_head; h.out_f32 = pl->Y; h.ld_f32 = pl->P;
     TRY((launch_gemm<A_LN, EPI_F32>(pl->tm_whead, pl->tm_whead, h, st)));
+    MARK(KC_HEAD);
     return DDC_OK;
 }
 
@@ -459,8 +501,9 @@ extern "C" int ddc_forward(ddc_plan* pl, const float* x, const int32_t* t, int32
     return DDC_OK;
 }
 
-static int enqueue_step(ddc_plan* pl, float* x, int B, float* x0_last, float* x0_seq, float* eps_seq, cudaStream_t st) {
-    TRY(enqueue_predictor(pl, x, B, nullptr, true, st));
+static int enqueue_step(ddc_plan* pl, float* x, int B, float* x0_last, float* x0_seq, float* eps_seq, cudaStream_t st,
+                        Prof* prof = nullptr) {
+    TRY(enqueue_predictor(pl, x, B, nullptr, true, st, prof));
     HeadDdimParams q{};
     q.y = pl->Y; q.ldy = pl->P; q.x = x;
     q.H = pl->sh.img_h; q.W = pl->sh.img_w; q.p = pl->sh.patch; q.L = pl->L; q.B = B;
@@ -468,7 +511,40 @@ static int enqueue_step(ddc_plan* pl, float* x, int B, float* x0_last, float* x0
     q.x0_last = x0_last; q.x0_seq = x0_seq; q.eps_seq = eps_seq;
     head_ddim_kernel<MODE_STEP><<<dim3(q.H / q.p, B), 256, head_ddim_smem(pl->sh), st>>>(q);
     CK(cudaGetLastError());
+    MARK(KC_DDIM);
     return DDC_OK;
+}
+
+extern "C" int ddc_profile_steps(ddc_plan* pl, float* x, int32_t batch, const ddc_step* host_table, int32_t n_steps,
+                                 float* class_ms, int32_t* class_launches, void* stream) {
+    TRY(check_call(pl, batch));
+    if (x == nullptr || host_table == nullptr || class_ms == nullptr || class_launches == nullptr)
+        return fail(DDC_E_INVALID, "NULL argument");
+    if (n_steps <= 0 || n_steps > pl->sh.total_steps) return fail(DDC_E_INVALID, "n_steps %d", n_steps);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(pl->device));
+    CK(cudaMemcpyAsync(pl->tbl, host_table, sizeof(StepEntry) * n_steps, cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(pl->ctr, 0, 2 * sizeof(int), st));
+    for (int c = 0; c < KC_COUNT; ++c) { class_ms[c] = 0.f; class_launches[c] = 0; }
+    Prof prof;
+    prof.st = st;
+    int rc = DDC_OK;
+    for (int i = 0; i < n_steps && rc == DDC_OK; ++i) {
+        rc = prof.begin();
+        if (rc == DDC_OK) rc = enqueue_step(pl, x, batch, nullptr, nullptr, nullptr, st, &prof);
+        if (rc != DDC_OK) break;
+        const cudaError_t e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) { rc = fail(DDC_E_CUDA, "profile: %s", cudaGetErrorString(e)); break; }
+        for (size_t j = 0; j < prof.cls.size(); ++j) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, prof.ev[j], prof.ev[j + 1]);
+            class_ms[prof.cls[j]] += ms;
+            class_launches[prof.cls[j]] += 1;
+        }
+        prof.release();
+    }
+    prof.release();
+    return rc;
 }
 
 extern "C" int ddc_sample(ddc_plan* pl, float* x, int32_t batch, const ddc_step* host_table, int32_t n_steps,

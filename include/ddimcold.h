@@ -104,6 +104,14 @@ int ddc_forward(ddc_plan* plan, const float* x, const int32_t* t, int32_t batch,
 int ddc_sample(ddc_plan* plan, float* x, int32_t batch, const ddc_step* host_table, int32_t n_steps, float* x0_last,
                float* x0_seq, float* eps_seq, int32_t use_graph, void* stream);
 
+/* Measurement aid (no reference counterpart): run `n_steps` steps of the loop with direct
+ * launches and a CUDA event between every kernel; accumulates device milliseconds and launch
+ * counts per kernel class into the HOST arrays class_ms[9] / class_launches[9], indexed
+ * 0 patchify, 1 patch-embed GEMM, 2 LN+qkv GEMM, 3 attention, 4 proj GEMM, 5 LN+fc1 GEMM,
+ * 6 fc2 GEMM, 7 LN+head GEMM, 8 unpatchify+clamp+DDIM.  Synchronises the stream. */
+int ddc_profile_steps(ddc_plan* plan, float* x, int32_t batch, const ddc_step* host_table, int32_t n_steps,
+                      float* class_ms, int32_t* class_launches, void* stream);
+
 /* Number of kernel launches one ddc_forward / one step of ddc_sample issues. */
 int ddc_launches_per_step(const ddc_plan* plan);
 
