@@ -14,7 +14,7 @@
 #include "attention.cuh"
 #include "common.cuh"
 #include "elementwise.cuh"
-#include "gemm_umma.cuh"
+#include "gemm2.cuh"
 
 using namespace ddc;
 
@@ -68,54 +68,77 @@ static int get_encode_fn(EncodeTiledFn* out) {
     return DDC_OK;
 }
 
-// bf16 [rows, cols] row-major, box = 64 columns x box_rows rows, 128-byte swizzle
-static int make_tmap(CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+// [rows, cols] row-major tensor, 128-byte swizzle; the box is 128 bytes wide (64 bf16 or 32 fp32)
+static int make_tmap(CUtensorMap* m, bool f32, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
     EncodeTiledFn enc;
     TRY(get_encode_fn(&enc));
-    if (cols % 64 != 0 || box_rows == 0 || box_rows > 256 || (reinterpret_cast<uintptr_t>(base) & 0xF) != 0)
-        return fail(DDC_E_INVALID, "tensor map: cols=%llu box_rows=%u base=%p", (unsigned long long)cols, box_rows, base);
+    const uint32_t box_cols = f32 ? 32 : 64;
+    const uint32_t esz = f32 ? 4 : 2;
+    if (cols % box_cols != 0 || rows == 0 || box_rows == 0 || box_rows > 256 || (reinterpret_cast<uintptr_t>(base) & 0xF) != 0)
+        return fail(DDC_E_INVALID, "tensor map: rows=%llu cols=%llu box_rows=%u base=%p", (unsigned long long)rows,
+                    (unsigned long long)cols, box_rows, base);
     cuuint64_t dims[2] = {cols, rows};
-    cuuint64_t strides[1] = {cols * 2};
-    cuuint32_t box[2] = {64, box_rows};
+    cuuint64_t strides[1] = {cols * esz};
+    cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = enc(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                     const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(DDC_E_CUDA, "cuTensorMapEncodeTiled -> %d", static_cast<int>(r));
     return DDC_OK;
 }
 
 // ------------------------------------------------------------------------------- GEMM launch
-static int pick_bn(int N) {
-    const int cands[] = {128, 96, 64, 48, 32, 16};
-    for (int c : cands)
-        if (N % c == 0) return c;
+static int pick_from(int N, const int* cands, int n) {
+    for (int i = 0; i < n; ++i)
+        if (N % cands[i] == 0) return cands[i];
     return 0;
 }
+static int pick_bn_stream(int N) { const int c[] = {256, 192, 128, 64}; return pick_from(N, c, 4); }
+static int pick_bn_f32(int N) { const int c[] = {256, 192, 128, 96, 64, 48, 32, 16}; return pick_from(N, c, 8); }
+static int pick_bn_row(int N) { const int c[] = {128, 64}; return pick_from(N, c, 2); }
 
-static int pick_stages(int K, int bn) {
-    const size_t budget = 200 * 1024;
-    const size_t a = static_cast<size_t>(K / GEMM_BK) * GEMM_A_KBLOCK_BYTES;
-    int s = static_cast<int>((budget - a) / (static_cast<size_t>(bn) * 128));
+static int pick_stages2(int K, int bn, bool rowblock) {
+    const long budget = 227 * 1024 - static_cast<long>(gemm2_smem_bytes(K, bn, 0, rowblock));
+    long s = budget / (static_cast<long>(bn) * 128);
     if (s > 6) s = 6;
-    return s;
+    return static_cast<int>(s);
 }
 
-template <int AMODE, int EPI>
-static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams p, cudaStream_t st) {
+static int num_sms() {
+    static int sms[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (sms[dev] == 0) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        sms[dev] = v;
+    }
+    return sms[dev];
+}
+
+template <int EPI>
+static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR,
+                        const CUtensorMap& tmN, Gemm2Params p, cudaStream_t st) {
     static int attr_dev_mask = 0;   // bit per device where the smem attribute has been raised
     int dev = 0;
     CK(cudaGetDevice(&dev));
     if (!(attr_dev_mask & (1 << dev))) {
-        CK(cudaFuncSetAttribute(gemm_umma_kernel<AMODE, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CK(cudaFuncSetAttribute(gemm2_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_dev_mask |= (1 << dev);
     }
-    if (p.K % GEMM_BK != 0 || p.K > 512 || p.bn % 16 != 0 || p.bn > 256 || p.N % p.bn != 0 || p.stages < 2)
-        return fail(DDC_E_INVALID, "gemm: unsupported M=%d N=%d K=%d bn=%d stages=%d", p.M, p.N, p.K, p.bn, p.stages);
-    const size_t smem = gemm_smem_bytes(p.K, p.bn, p.stages);
+    constexpr bool rowblock = (EPI == R_RESID || EPI == R_EMBED);
+    const bool bn_ok = (EPI == S_F32) ? (p.bn % 16 == 0) : (rowblock ? (p.bn % 32 == 0) : (p.bn % 64 == 0));
+    if (p.K % G2_BK != 0 || p.K > 512 || !bn_ok || p.bn > 256 || p.bn <= 0 || p.N % p.bn != 0 || p.stages < 2 ||
+        p.stages > 8 || (rowblock && (p.N > 512 || p.N / p.bn > 4 || p.N % 64 != 0)))
+        return fail(DDC_E_INVALID, "gemm: unsupported M=%d N=%d K=%d bn=%d stages=%d epi=%d", p.M, p.N, p.K, p.bn,
+                    p.stages, EPI);
+    const size_t smem = gemm2_smem_bytes(p.K, p.bn, p.stages, rowblock);
     if (smem > 227 * 1024) return fail(DDC_E_INVALID, "gemm: %zu B of shared memory needed", smem);
-    const int grid = (p.M + GEMM_BM - 1) / GEMM_BM;
-    gemm_umma_kernel<AMODE, EPI><<<grid, GEMM_THREADS, smem, st>>>(tmA, tmB, p);
+    p.num_tiles = (p.M + G2_BM - 1) / G2_BM;
+    const int sms = num_sms();
+    const int grid = p.num_tiles < sms ? p.num_tiles : sms;
+    gemm2_kernel<EPI><<<grid, G2_THREADS, smem, st>>>(tmA, tmB, tmO, tmR, tmN, p);
     CK(cudaGetLastError());
     return DDC_OK;
 }
@@ -181,7 +204,7 @@ struct ddc_plan {
     ddc_shape sh;
     int maxB, device;
     int L, n, P, C, Kp, Mpad;
-    int bn_qkv, bn_c, bn_head;
+    int bn_qkv, bn_fc1, bn_row, bn_head;
     bool packed;
     // weight arena
     bf16* w_patch;
@@ -193,11 +216,15 @@ struct ddc_plan {
     CUtensorMap tm_wpatch, tm_whead;
     // work arena
     float* X;
-    bf16 *QKV, *O, *Hd, *Ap;
+    bf16 *QKV, *O, *Hd, *Ap, *XN;
     float* Y;
     StepEntry* tbl;
     int* ctr;
-    CUtensorMap tm_Ap, tm_O, tm_Hd;
+    CUtensorMap tm_Ap, tm_O, tm_Hd, tm_XN;   // A-operand loads (box 64 x 128, padded row count)
+    CUtensorMap tm_Xld;                      // residual loads (fp32, box 32 x 32, padded row count)
+    // store maps are clipped to exactly batch*L rows, so they are rebuilt when the batch changes
+    int maps_B;
+    CUtensorMap st_QKV, st_Hd, st_XN, st_X;
     // graph cache
     cudaGraphExec_t gexec;
     GraphKey gkey;
@@ -258,6 +285,7 @@ static void carve(ddc_plan* pl, void* weight_arena, void* work_arena, size_t* wb
     pl->O = k.take<bf16>(Mp * C);
     pl->Hd = k.take<bf16>(Mp * C);
     pl->Ap = k.take<bf16>(Mp * Kp);
+    pl->XN = k.take<bf16>(Mp * C);
     pl->Y = k.take<float>(Mp * P);
     pl->tbl = k.take<StepEntry>(s.total_steps);
     pl->ctr = k.take<int>(64);
@@ -272,10 +300,11 @@ static void derive(ddc_plan* pl, const ddc_shape* s, int max_batch) {
     pl->P = 3 * s->patch * s->patch;
     pl->C = s->embed;
     pl->Kp = (pl->P + 63) / 64 * 64;
-    pl->Mpad = (max_batch * pl->L + GEMM_BM - 1) / GEMM_BM * GEMM_BM;
-    pl->bn_qkv = pick_bn(3 * pl->C);
-    pl->bn_c = pick_bn(pl->C);
-    pl->bn_head = pick_bn(pl->P);
+    pl->Mpad = (max_batch * pl->L + G2_BM - 1) / G2_BM * G2_BM;
+    pl->bn_qkv = pick_bn_stream(3 * pl->C);
+    pl->bn_fc1 = pick_bn_stream(pl->C);
+    pl->bn_row = pick_bn_row(pl->C);
+    pl->bn_head = pick_bn_f32(pl->P);
 }
 
 extern "C" int ddc_arena_bytes(const ddc_shape* shape, int32_t max_batch, size_t* weight_bytes, size_t* work_bytes) {
@@ -317,19 +346,22 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
     }
     const uint64_t C = pl->C, Mp = pl->Mpad;
     int r = DDC_OK;
-    auto mk = [&](CUtensorMap* m, const void* base, uint64_t rows, uint64_t cols, uint32_t box) {
-        if (r == DDC_OK) r = make_tmap(m, base, rows, cols, box);
+    auto mk = [&](CUtensorMap* m, bool f32, const void* base, uint64_t rows, uint64_t cols, uint32_t box) {
+        if (r == DDC_OK) r = make_tmap(m, f32, base, rows, cols, box);
     };
-    mk(&pl->tm_Ap, pl->Ap, Mp, pl->Kp, GEMM_BM);
-    mk(&pl->tm_O, pl->O, Mp, C, GEMM_BM);
-    mk(&pl->tm_Hd, pl->Hd, Mp, C, GEMM_BM);
-    mk(&pl->tm_wpatch, pl->w_patch, C, pl->Kp, pl->bn_c);
-    mk(&pl->tm_whead, pl->w_head, pl->P, C, pl->bn_head);
+    pl->maps_B = 0;
+    mk(&pl->tm_Ap, false, pl->Ap, Mp, pl->Kp, G2_BM);
+    mk(&pl->tm_O, false, pl->O, Mp, C, G2_BM);
+    mk(&pl->tm_Hd, false, pl->Hd, Mp, C, G2_BM);
+    mk(&pl->tm_XN, false, pl->XN, Mp, C, G2_BM);
+    mk(&pl->tm_Xld, true, pl->X, Mp, C, 32);
+    mk(&pl->tm_wpatch, false, pl->w_patch, C, pl->Kp, pl->bn_row);
+    mk(&pl->tm_whead, false, pl->w_head, pl->P, C, pl->bn_head);
     for (auto& l : pl->layers) {
-        mk(&l.tm_qkv, l.w_qkv, 3 * C, C, pl->bn_qkv);
-        mk(&l.tm_proj, l.w_proj, C, C, pl->bn_c);
-        mk(&l.tm_fc1, l.w_fc1, C, C, pl->bn_c);
-        mk(&l.tm_fc2, l.w_fc2, C, C, pl->bn_c);
+        mk(&l.tm_qkv, false, l.w_qkv, 3 * C, C, pl->bn_qkv);
+        mk(&l.tm_proj, false, l.w_proj, C, C, pl->bn_row);
+        mk(&l.tm_fc1, false, l.w_fc1, C, C, pl->bn_fc1);
+        mk(&l.tm_fc2, false, l.w_fc2, C, C, pl->bn_row);
     }
     if (r != DDC_OK) {
         delete pl;
@@ -424,54 +456,69 @@ struct Prof {
 // ------------------------------------------------------------------------------- one predictor evaluation
 // Enqueues: patchify -> embed GEMM -> depth x [LN1+qkv GEMM, attention, proj GEMM(+res),
 // LN2+fc1 GEMM(+GELU), fc2 GEMM(+res)] -> LN+head GEMM.  Leaves the head output in pl->Y.
+static int ensure_store_maps(ddc_plan* pl, int B) {
+    if (pl->maps_B == B) return DDC_OK;
+    const uint64_t M = static_cast<uint64_t>(B) * pl->L, C = pl->C;
+    TRY(make_tmap(&pl->st_QKV, false, pl->QKV, M, 3 * C, 32));
+    TRY(make_tmap(&pl->st_Hd, false, pl->Hd, M, C, 32));
+    TRY(make_tmap(&pl->st_XN, false, pl->XN, M, C, 32));
+    TRY(make_tmap(&pl->st_X, true, pl->X, M, C, 32));
+    pl->maps_B = B;
+    if (pl->gexec) {                 // the captured graph holds the old maps by value
+        cudaGraphExecDestroy(pl->gexec);
+        pl->gexec = nullptr;
+    }
+    return DDC_OK;
+}
+
+// Enqueues: patchify -> patch-embed GEMM (+cls/pos/time, emits LN1(0)) -> depth x [qkv GEMM,
+// attention, proj GEMM (+residual, emits LN2), fc1 GEMM (+GELU), fc2 GEMM (+residual, emits the
+// next LayerNorm)] -> head GEMM.  Leaves the head output in pl->Y.
 static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_img, bool use_step_ctr, cudaStream_t st,
                              Prof* prof = nullptr) {
     const ddc_shape& s = pl->sh;
     const int C = pl->C, L = pl->L, M = B * L;
+    TRY(ensure_store_maps(pl, B));
     patchify_kernel<<<dim3(s.img_h / s.patch, B), 256, 0, st>>>(x, pl->Ap, s.img_h, s.img_w, s.patch, L, pl->Kp,
                                                                   use_step_ctr ? pl->ctr : nullptr);
     CK(cudaGetLastError());
     MARK(KC_PATCHIFY);
-    GemmParams g{};
-    g.M = M;
-    g.ln_eps = 1e-5f;
-    // patch embed + cls/pos/time
-    g.N = C; g.K = pl->Kp; g.bn = pl->bn_c; g.stages = pick_stages(g.K, g.bn);
-    g.out_f32 = pl->X; g.ld_f32 = C;
-    g.posb = pl->posb; g.L = L; g.time_tab = pl->time_tab; g.t_img = t_img; g.tbl = pl->tbl; g.cur = pl->ctr;
-    TRY((launch_gemm<A_TMA, EPI_EMBED>(pl->tm_Ap, pl->tm_wpatch, g, st)));
+    const LayerW& l0 = pl->layers[0];
+    Gemm2Params g{};
+    g.M = M; g.N = C; g.K = pl->Kp; g.bn = pl->bn_row; g.stages = pick_stages2(g.K, g.bn, true);
+    g.ln_g = l0.ln1_g; g.ln_b = l0.ln1_b; g.ln_eps = 1e-5f;
+    g.posb = pl->posb; g.L = L; g.time_tab = pl->time_tab; g.t_img = t_img; g.tbl = pl->tbl; g.cur = pl->ctr; g.B = B;
+    TRY((launch_gemm2<R_EMBED>(pl->tm_Ap, pl->tm_wpatch, pl->st_X, pl->tm_Xld, pl->st_XN, g, st)));
     MARK(KC_EMBED);
     for (int i = 0; i < s.depth; ++i) {
         LayerW& l = pl->layers[i];
-        GemmParams q{};
-        q.M = M; q.ln_eps = 1e-5f;
-        q.N = 3 * C; q.K = C; q.bn = pl->bn_qkv; q.stages = pick_stages(q.K, q.bn);
-        q.x = pl->X; q.ldx = C; q.ln_g = l.ln1_g; q.ln_b = l.ln1_b;
-        q.bias = l.b_qkv; q.out_bf16 = pl->QKV; q.ld_bf16 = 3 * C;
-        TRY((launch_gemm<A_LN, EPI_BF16>(l.tm_qkv, l.tm_qkv, q, st)));
+        Gemm2Params q{};
+        q.M = M; q.N = 3 * C; q.K = C; q.bn = pl->bn_qkv; q.stages = pick_stages2(q.K, q.bn, false);
+        q.bias = l.b_qkv;
+        TRY((launch_gemm2<S_BF16>(pl->tm_XN, l.tm_qkv, pl->st_QKV, pl->tm_Xld, pl->st_XN, q, st)));
         MARK(KC_QKV);
         TRY(run_attention(pl->QKV, pl->O, B, L, C, s.heads, st));
         MARK(KC_ATTN);
-        GemmParams r{};
-        r.M = M; r.N = C; r.K = C; r.bn = pl->bn_c; r.stages = pick_stages(r.K, r.bn);
-        r.bias = l.b_proj; r.out_f32 = pl->X; r.ld_f32 = C;
-        TRY((launch_gemm<A_TMA, EPI_RESID>(pl->tm_O, l.tm_proj, r, st)));
+        Gemm2Params r{};
+        r.M = M; r.N = C; r.K = C; r.bn = pl->bn_row; r.stages = pick_stages2(r.K, r.bn, true);
+        r.bias = l.b_proj; r.ln_g = l.ln2_g; r.ln_b = l.ln2_b; r.ln_eps = 1e-5f;
+        TRY((launch_gemm2<R_RESID>(pl->tm_O, l.tm_proj, pl->st_X, pl->tm_Xld, pl->st_XN, r, st)));
         MARK(KC_PROJ);
-        GemmParams f{};
-        f.M = M; f.ln_eps = 1e-5f; f.N = C; f.K = C; f.bn = pl->bn_c; f.stages = pick_stages(f.K, f.bn);
-        f.x = pl->X; f.ldx = C; f.ln_g = l.ln2_g; f.ln_b = l.ln2_b;
-        f.bias = l.b_fc1; f.out_bf16 = pl->Hd; f.ld_bf16 = C;
-        TRY((launch_gemm<A_LN, EPI_BF16_GELU>(l.tm_fc1, l.tm_fc1, f, st)));
+        Gemm2Params f{};
+        f.M = M; f.N = C; f.K = C; f.bn = pl->bn_fc1; f.stages = pick_stages2(f.K, f.bn, false);
+        f.bias = l.b_fc1;
+        TRY((launch_gemm2<S_BF16_GELU>(pl->tm_XN, l.tm_fc1, pl->st_Hd, pl->tm_Xld, pl->st_XN, f, st)));
         MARK(KC_FC1);
         r.bias = l.b_fc2;
-        TRY((launch_gemm<A_TMA, EPI_RESID>(pl->tm_Hd, l.tm_fc2, r, st)));
+        r.ln_g = (i + 1 < s.depth) ? pl->layers[i + 1].ln1_g : pl->lnf_g;
+        r.ln_b = (i + 1 < s.depth) ? pl->layers[i + 1].ln1_b : pl->lnf_b;
+        TRY((launch_gemm2<R_RESID>(pl->tm_Hd, l.tm_fc2, pl->st_X, pl->tm_Xld, pl->st_XN, r, st)));
         MARK(KC_FC2);
     }
-    GemmParams h{};
-    h.M = M; h.ln_eps = 1e-5f; h.N = pl->P; h.K = C; h.bn = pl->bn_head; h.stages = pick_stages(h.K, h.bn);
-    h.x = pl->X; h.ldx = C; h.ln_g = pl->lnf_g; h.ln_b = pl->lnf_b;
+    Gemm2Params h{};
+    h.M = M; h.N = pl->P; h.K = C; h.bn = pl->bn_head; h.stages = pick_stages2(h.K, h.bn, false);
     h.bias = pl->b_head; h.out_f32 = pl->Y; h.ld_f32 = pl->P;
-    TRY((launch_gemm<A_LN, EPI_F32>(pl->tm_whead, pl->tm_whead, h, st)));
+    TRY((launch_gemm2<S_F32>(pl->tm_XN, pl->tm_whead, pl->st_XN, pl->tm_Xld, pl->st_XN, h, st)));
     MARK(KC_HEAD);
     return DDC_OK;
 }
@@ -643,41 +690,52 @@ extern "C" int ddc_cold_table(ddc_step* tab, int32_t capacity, int32_t* n_steps)
 }
 
 // ------------------------------------------------------------------------------- kernel-level entries
-extern "C" int ddc_k_gemm(int32_t amode, int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const float* ln_g,
-                          const float* ln_b, const void* W, const float* bias, void* out, int32_t ld_out, void* stream) {
+extern "C" int ddc_k_gemm(int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const void* W, const float* bias,
+                          void* out, int32_t ld_out, void* stream) {
     if (A == nullptr || W == nullptr || bias == nullptr || out == nullptr) return fail(DDC_E_INVALID, "NULL tensor");
-    if (M <= 0 || N <= 0 || K <= 0) return fail(DDC_E_INVALID, "bad sizes");
+    if (M <= 0 || N <= 0 || K <= 0 || K % 64 != 0 || ld_out != N) return fail(DDC_E_INVALID, "bad sizes");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    const int bn = pick_bn(N);
-    if (bn == 0) return fail(DDC_E_INVALID, "N=%d must be a multiple of 16", N);
-    const uint64_t Mp = (static_cast<uint64_t>(M) + GEMM_BM - 1) / GEMM_BM * GEMM_BM;
-    CUtensorMap tmA, tmB;
-    TRY(make_tmap(&tmB, W, N, K, bn));
-    GemmParams p{};
-    p.M = M; p.N = N; p.K = K; p.bn = bn; p.stages = pick_stages(K, bn); p.ln_eps = 1e-5f;
-    p.bias = bias;
-    if (epi == EPI_BF16 || epi == EPI_BF16_GELU) { p.out_bf16 = static_cast<bf16*>(out); p.ld_bf16 = ld_out; }
-    else { p.out_f32 = static_cast<float*>(out); p.ld_f32 = ld_out; }
-    if (amode == A_LN) {
-        if (ln_g == nullptr || ln_b == nullptr) return fail(DDC_E_INVALID, "LayerNorm parameters are NULL");
-        p.x = static_cast<const float*>(A); p.ldx = K; p.ln_g = ln_g; p.ln_b = ln_b;
-        tmA = tmB;
-        switch (epi) {
-            case EPI_BF16: return launch_gemm<A_LN, EPI_BF16>(tmA, tmB, p, st);
-            case EPI_BF16_GELU: return launch_gemm<A_LN, EPI_BF16_GELU>(tmA, tmB, p, st);
-            case EPI_RESID: return launch_gemm<A_LN, EPI_RESID>(tmA, tmB, p, st);
-            case EPI_F32: return launch_gemm<A_LN, EPI_F32>(tmA, tmB, p, st);
-        }
-    } else if (amode == A_TMA) {
-        TRY(make_tmap(&tmA, A, Mp, K, GEMM_BM));
-        switch (epi) {
-            case EPI_BF16: return launch_gemm<A_TMA, EPI_BF16>(tmA, tmB, p, st);
-            case EPI_BF16_GELU: return launch_gemm<A_TMA, EPI_BF16_GELU>(tmA, tmB, p, st);
-            case EPI_RESID: return launch_gemm<A_TMA, EPI_RESID>(tmA, tmB, p, st);
-            case EPI_F32: return launch_gemm<A_TMA, EPI_F32>(tmA, tmB, p, st);
-        }
+    const uint64_t Mp = (static_cast<uint64_t>(M) + G2_BM - 1) / G2_BM * G2_BM;
+    const int bn = (epi == S_F32) ? pick_bn_f32(N) : pick_bn_stream(N);
+    if (bn == 0) return fail(DDC_E_INVALID, "N=%d must be a multiple of %d", N, epi == S_F32 ? 16 : 64);
+    CUtensorMap tmA, tmB, tmO;
+    TRY(make_tmap(&tmA, false, A, Mp, K, G2_BM));
+    TRY(make_tmap(&tmB, false, W, N, K, bn));
+    Gemm2Params p{};
+    p.M = M; p.N = N; p.K = K; p.bn = bn; p.stages = pick_stages2(K, bn, false); p.bias = bias;
+    switch (epi) {
+        case S_BF16:
+            TRY(make_tmap(&tmO, false, out, M, N, 32));
+            return launch_gemm2<S_BF16>(tmA, tmB, tmO, tmA, tmA, p, st);
+        case S_BF16_GELU:
+            TRY(make_tmap(&tmO, false, out, M, N, 32));
+            return launch_gemm2<S_BF16_GELU>(tmA, tmB, tmO, tmA, tmA, p, st);
+        case S_F32:
+            p.out_f32 = static_cast<float*>(out); p.ld_f32 = ld_out;
+            return launch_gemm2<S_F32>(tmA, tmB, tmA, tmA, tmA, p, st);
     }
-    return fail(DDC_E_INVALID, "amode=%d epi=%d", amode, epi);
+    return fail(DDC_E_INVALID, "epi=%d", epi);
+}
+
+extern "C" int ddc_k_gemm_resid_ln(int32_t M, int32_t C, int32_t K, const void* A, const void* W, const float* bias,
+                                   float* x, const float* ln_g, const float* ln_b, void* xn, void* stream) {
+    if (A == nullptr || W == nullptr || bias == nullptr || x == nullptr || ln_g == nullptr || ln_b == nullptr ||
+        xn == nullptr)
+        return fail(DDC_E_INVALID, "NULL tensor");
+    if (M <= 0 || C <= 0 || K <= 0 || K % 64 != 0 || C % 64 != 0 || C > 512) return fail(DDC_E_INVALID, "bad sizes");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const uint64_t Mp = (static_cast<uint64_t>(M) + G2_BM - 1) / G2_BM * G2_BM;
+    const int bn = pick_bn_row(C);
+    CUtensorMap tmA, tmB, tmO, tmR, tmN;
+    TRY(make_tmap(&tmA, false, A, Mp, K, G2_BM));
+    TRY(make_tmap(&tmB, false, W, C, K, bn));
+    TRY(make_tmap(&tmO, true, x, M, C, 32));
+    TRY(make_tmap(&tmR, true, x, Mp, C, 32));
+    TRY(make_tmap(&tmN, false, xn, M, C, 32));
+    Gemm2Params p{};
+    p.M = M; p.N = C; p.K = K; p.bn = bn; p.stages = pick_stages2(K, bn, true); p.bias = bias;
+    p.ln_g = ln_g; p.ln_b = ln_b; p.ln_eps = 1e-5f;
+    return launch_gemm2<R_RESID>(tmA, tmB, tmO, tmR, tmN, p, st);
 }
 
 extern "C" int ddc_k_attention(const void* qkv, void* out, int32_t batch, int32_t L, int32_t C, int32_t heads,

@@ -1,0 +1,412 @@
+// Persistent token GEMM on the 5th-gen tensor cores, everything moved by TMA.
+//
+//   OUT[M, N] = epilogue( A[M, K] * W[N, K]^T ),  A and W bf16 K-major, K <= 512.
+//
+// A CTA (one per SM) walks 128-row M tiles round-robin.  Roles: warp 0 = TMA producer (the A
+// tile, K/64 boxes of 64x128, then the W tiles bn x 64 through a ring), warp 1 = tcgen05.mma
+// issuer (M=128, N=bn, K=16 per instruction, fp32 accumulators in TMEM), warp 2 = TMEM
+// allocator, warps 4-7 = epilogue (thread = one output row).  A is released K-block by
+// K-block while the last N tile is being multiplied, so the next tile's A loads overlap it.
+//
+// Two flavours:
+//  * stream  (S_*): N tiles alternate between two TMEM accumulator stages; the epilogue
+//    converts to bf16 in 32x128-byte staging slots and hands them to TMA stores.
+//      S_BF16       out = bf16(acc + bias)                        qkv   (ViT.py:107)
+//      S_BF16_GELU  out = bf16(gelu_erf(acc + bias))              fc1   (ViT.py:85-86)
+//      S_F32        out = acc + bias  (fp32, direct stores)       head  (ViT.py:213)
+//  * row-block (R_*): N == embed_dim, the whole 128 x C fp32 row block lives in TMEM.
+//      pass 1  v = acc + bias + X   (R_RESID, X prefetched by TMA; ViT.py:136-137)
+//              v = acc + posb[l] + time[t]  (R_EMBED; ViT.py:154,202-205)
+//              v -> X (fp32, TMA store), v -> back into TMEM, row sum
+//      pass 2  exact two-pass variance from TMEM
+//      pass 3  XN = bf16(LayerNorm(v) * g + b) -> TMA store.  XN is the *next* GEMM's A
+//              operand, so LayerNorm (ViT.py:133,137,212) never costs its own pass over HBM.
+#pragma once
+
+#include "common.cuh"
+
+namespace ddc {
+
+enum { S_BF16 = 0, S_BF16_GELU = 1, S_F32 = 2, R_RESID = 3, R_EMBED = 4 };
+
+constexpr int G2_BM = 128;
+constexpr int G2_BK = 64;
+constexpr int G2_THREADS = 256;
+constexpr int G2_A_KB_BYTES = G2_BM * 128;
+constexpr int G2_SLOT_BYTES = 32 * 128;     // one epilogue warp's staging unit: 32 rows x 128 B
+constexpr int G2_ES_STREAM = 2;             // staging slots per epilogue warp
+constexpr int G2_ES_ROW = 4;
+constexpr int G2_PD_ROW = 2;                // residual chunks prefetched ahead per warp
+
+struct Gemm2Params {
+    int M, N, K, bn, stages, num_tiles;
+    const float* bias;
+    float* out_f32;          // S_F32
+    int ld_f32;
+    const float* ln_g;       // R_*: parameters of the LayerNorm that FOLLOWS this GEMM
+    const float* ln_b;
+    float ln_eps;
+    const float* posb;       // R_EMBED
+    int L;
+    const float* time_tab;
+    const int* t_img;
+    const StepEntry* tbl;
+    const int* cur;
+    int B;
+};
+
+__host__ __device__ inline uint32_t g2_pow2_cols(uint32_t c) {
+    uint32_t p = 32;
+    while (p < c) p <<= 1;
+    return p;
+}
+
+inline size_t gemm2_smem_bytes(int K, int bn, int stages, bool rowblock) {
+    return 1024 + static_cast<size_t>(K / G2_BK) * G2_A_KB_BYTES + static_cast<size_t>(stages) * bn * 128 +
+           static_cast<size_t>(4) * (rowblock ? G2_ES_ROW : G2_ES_STREAM) * G2_SLOT_BYTES + 512;
+}
+
+// byte offset of 16-byte chunk `j` of row `r` inside a 128-byte-swizzled 32-row slot
+__device__ __forceinline__ uint32_t slot_off(int r, int j) { return r * 128 + ((j ^ (r & 7)) << 4); }
+
+template <int EPI>
+__global__ void __launch_bounds__(G2_THREADS, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR,
+             const __grid_constant__ CUtensorMap tmN, const Gemm2Params p) {
+    constexpr bool ROWBLOCK = (EPI == R_RESID || EPI == R_EMBED);
+    constexpr int ES = ROWBLOCK ? G2_ES_ROW : G2_ES_STREAM;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+    const int kblocks = p.K / G2_BK;
+    const int num_nt = p.N / p.bn;
+    const uint32_t b_stage_bytes = static_cast<uint32_t>(p.bn) * 128u;
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem_a + static_cast<size_t>(kblocks) * G2_A_KB_BYTES;
+    uint8_t* smem_e = smem_b + static_cast<size_t>(p.stages) * b_stage_bytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_e + 4 * ES * G2_SLOT_BYTES);
+    uint64_t* full_bar = bars;             // [8]  W ring: TMA -> MMA
+    uint64_t* empty_bar = bars + 8;        // [8]  W ring: MMA -> TMA
+    uint64_t* afull_bar = bars + 16;       // [8]  A K-block landed
+    uint64_t* aempty_bar = bars + 24;      // [8]  A K-block no longer needed by this tile
+    uint64_t* tfull_bar = bars + 32;       // [4]  accumulator stage / N tile complete
+    uint64_t* tempty_bar = bars + 36;      // [2]  accumulator drained
+    uint64_t* res_bar = bars + 38;         // [16] residual chunk landed (per epilogue warp x slot)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 54);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t acc_stride = g2_pow2_cols(p.bn);
+    const uint32_t tmem_cols = ROWBLOCK ? g2_pow2_cols(p.N) : g2_pow2_cols(2 * acc_stride);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        if (EPI != S_F32) tma_prefetch_desc(&tmO);
+        if (EPI == R_RESID) tma_prefetch_desc(&tmR);
+        if (ROWBLOCK) tma_prefetch_desc(&tmN);
+        for (int i = 0; i < 8; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+            mbar_init(&afull_bar[i], 1);
+            mbar_init(&aempty_bar[i], 1);
+        }
+        for (int i = 0; i < 4; ++i) mbar_init(&tfull_bar[i], 1);
+        mbar_init(&tempty_bar[0], 4);
+        mbar_init(&tempty_bar[1], 4);
+        for (int i = 0; i < 16; ++i) mbar_init(&res_bar[i], 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) {
+        tmem_alloc(tmem_slot, tmem_cols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================================================= TMA producer
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0, tcount = 0;
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+                const int m0 = tile * G2_BM;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    mbar_wait(&aempty_bar[kb], (tcount & 1) ^ 1);
+                    mbar_arrive_expect_tx(&afull_bar[kb], G2_A_KB_BYTES);
+                    tma_load_2d(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0);
+                }
+                for (int nt = 0; nt < num_nt; ++nt) {
+                    for (int kb = 0; kb < kblocks; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        mbar_arrive_expect_tx(&full_bar[stage], b_stage_bytes);
+                        tma_load_2d(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
+                                    kb * G2_BK, nt * p.bn);
+                        if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ================================================================= MMA issuer
+        const uint32_t idesc = umma_idesc_bf16(G2_BM, static_cast<uint32_t>(p.bn));
+        const uint32_t a_base = smem_u32(smem_a);
+        const uint32_t b_base = smem_u32(smem_b);
+        uint32_t stage = 0, phase = 0, tcount = 0, acc_it = 0;
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+            for (int nt = 0; nt < num_nt; ++nt) {
+                uint32_t d_tmem;
+                uint64_t* done_bar;
+                if (ROWBLOCK) {
+                    if (nt == 0) mbar_wait(&tempty_bar[0], (tcount & 1) ^ 1);
+                    d_tmem = tmem_base + static_cast<uint32_t>(nt * p.bn);
+                    done_bar = &tfull_bar[nt];
+                } else {
+                    const uint32_t acc = acc_it & 1;
+                    mbar_wait(&tempty_bar[acc], ((acc_it >> 1) & 1) ^ 1);
+                    d_tmem = tmem_base + acc * acc_stride;
+                    done_bar = &tfull_bar[acc];
+                    ++acc_it;
+                }
+                tc_fence_after();
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    if (nt == 0) mbar_wait(&afull_bar[kb], tcount & 1);
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+#pragma unroll
+                        for (int k = 0; k < G2_BK / 16; ++k) {
+                            const uint64_t ad = umma_desc_sw128(a_base + kb * G2_A_KB_BYTES + k * 32);
+                            const uint64_t bd = umma_desc_sw128(b_base + stage * b_stage_bytes + k * 32);
+                            umma_bf16_ss(d_tmem, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
+                        }
+                        umma_commit(&empty_bar[stage]);
+                        if (nt == num_nt - 1) umma_commit(&aempty_bar[kb]);
+                        if (kb == kblocks - 1) umma_commit(done_bar);
+                    }
+                    __syncwarp();
+                    if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= 4) {
+        // ================================================================= epilogue
+        const int q = warp - 4;
+        uint8_t* my_slots = smem_e + static_cast<size_t>(q) * ES * G2_SLOT_BYTES;
+        const uint32_t lane_taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+        uint32_t tcount = 0;
+        if (!ROWBLOCK) {
+            uint32_t acc_it = 0, slot_it = 0;
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+                const int row0 = tile * G2_BM + q * 32;
+                const int row = row0 + lane;
+                for (int nt = 0; nt < num_nt; ++nt, ++acc_it) {
+                    const uint32_t acc = acc_it & 1;
+                    mbar_wait(&tfull_bar[acc], (acc_it >> 1) & 1);
+                    tc_fence_after();
+                    const uint32_t t_row = lane_taddr + acc * acc_stride;
+                    if (EPI == S_F32) {
+                        for (int c = 0; c < p.bn; c += 16) {
+                            float v[16];
+                            tmem_ld16(t_row + c, v);
+                            if (row < p.M) {
+                                const int n0 = nt * p.bn + c;
+                                float4* dst = reinterpret_cast<float4*>(p.out_f32 + static_cast<size_t>(row) * p.ld_f32 + n0);
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) {
+                                    const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + 4 * i));
+                                    dst[i] = make_float4(v[4 * i] + b.x, v[4 * i + 1] + b.y, v[4 * i + 2] + b.z,
+                                                         v[4 * i + 3] + b.w);
+                                }
+                            }
+                        }
+                    } else {
+                        for (int c = 0; c < p.bn; c += 64, ++slot_it) {
+                            uint8_t* slot = my_slots + (slot_it % ES) * G2_SLOT_BYTES;
+                            if (lane == 0) bulk_wait_read<ES - 1>();      // this slot's previous store has read it
+                            __syncwarp();
+                            const int n0 = nt * p.bn + c;
+#pragma unroll
+                            for (int h = 0; h < 2; ++h) {
+                                float v[32];
+                                tmem_ld32(t_row + c + 32 * h, v);
+#pragma unroll
+                                for (int i = 0; i < 32; i += 4) {
+                                    const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + 32 * h + i));
+                                    v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
+                                }
+                                if (EPI == S_BF16_GELU) {
+#pragma unroll
+                                    for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+                                }
+#pragma unroll
+                                for (int j = 0; j < 4; ++j) {
+                                    uint4 o;
+                                    o.x = pack_bf16(v[8 * j], v[8 * j + 1]);
+                                    o.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
+                                    o.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]);
+                                    o.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+                                    *reinterpret_cast<uint4*>(slot + slot_off(lane, 4 * h + j)) = o;
+                                }
+                            }
+                            fence_proxy_async_smem();
+                            __syncwarp();
+                            if (lane == 0 && row0 < p.M) {
+                                tma_store_2d(&tmO, slot, n0, row0);
+                                bulk_commit();
+                            }
+                        }
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+                }
+            }
+        } else {
+            // ---------------------------------------------------------- row-block flavour
+            const int nchunk = p.N / 32;            // fp32 chunks of 128 B per row
+            const float inv_n = 1.0f / static_cast<float>(p.N);
+            uint32_t ri = 0;                        // residual / staging slot counter (this warp)
+            uint32_t loads = 0;                     // residual loads issued so far (lane 0 bookkeeping = all lanes)
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+                const int row0 = tile * G2_BM + q * 32;
+                const int row = row0 + lane;
+                const float* embed_pos = nullptr;
+                const float* embed_time = nullptr;
+                if (EPI == R_EMBED) {
+                    int b = row / p.L;
+                    const int l = row - b * p.L;
+                    if (b > p.B - 1) b = p.B - 1;
+                    const int t = p.t_img ? p.t_img[b] : p.tbl[*p.cur].t;
+                    embed_pos = p.posb + static_cast<size_t>(l) * p.N;
+                    embed_time = p.time_tab + static_cast<size_t>(t) * p.N;
+                }
+                if (EPI == R_RESID) {
+                    // slots may still be the source of the previous tile's XN stores
+                    if (lane == 0) {
+                        bulk_wait_read<0>();
+                        for (int c = 0; c < G2_PD_ROW && c < nchunk; ++c) {
+                            const uint32_t s = (ri + c) % ES;
+                            mbar_arrive_expect_tx(&res_bar[q * ES + s], G2_SLOT_BYTES);
+                            tma_load_2d(my_slots + s * G2_SLOT_BYTES, &tmR, &res_bar[q * ES + s], c * 32, row0);
+                        }
+                    }
+                    __syncwarp();
+                }
+                float sum = 0.f;
+                for (int c = 0; c < nchunk; ++c, ++ri) {
+                    const uint32_t s = ri % ES;
+                    uint8_t* slot = my_slots + s * G2_SLOT_BYTES;
+                    if (lane == 0) {
+                        bulk_wait_read<1>();        // every store but the most recent has released its slot
+                        if (EPI == R_RESID && c + G2_PD_ROW < nchunk) {
+                            const uint32_t s2 = (ri + G2_PD_ROW) % ES;
+                            mbar_arrive_expect_tx(&res_bar[q * ES + s2], G2_SLOT_BYTES);
+                            tma_load_2d(my_slots + s2 * G2_SLOT_BYTES, &tmR, &res_bar[q * ES + s2],
+                                        (c + G2_PD_ROW) * 32, row0);
+                        }
+                    }
+                    __syncwarp();
+                    const int n0 = c * 32;
+                    if (n0 % p.bn == 0) {
+                        mbar_wait(&tfull_bar[n0 / p.bn], tcount & 1);
+                        tc_fence_after();
+                    }
+                    float v[32];
+                    tmem_ld32(lane_taddr + n0, v);
+                    if (EPI == R_RESID) {
+                        // per-slot phase: this warp has waited on slot s exactly (loads_done_on_s) times
+                        mbar_wait(&res_bar[q * ES + s], (loads / ES) & 1);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 r = *reinterpret_cast<const float4*>(slot + slot_off(lane, j));
+                            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + 4 * j));
+                            v[4 * j] += r.x + b.x; v[4 * j + 1] += r.y + b.y;
+                            v[4 * j + 2] += r.z + b.z; v[4 * j + 3] += r.w + b.w;
+                        }
+                        ++loads;
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 a = __ldg(reinterpret_cast<const float4*>(embed_pos + n0 + 4 * j));
+                            const float4 b = __ldg(reinterpret_cast<const float4*>(embed_time + n0 + 4 * j));
+                            v[4 * j] += a.x + b.x; v[4 * j + 1] += a.y + b.y;
+                            v[4 * j + 2] += a.z + b.z; v[4 * j + 3] += a.w + b.w;
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) sum += v[i];
+                    tmem_st32(lane_taddr + n0, v);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        *reinterpret_cast<float4*>(slot + slot_off(lane, j)) =
+                            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0 && row0 < p.M) {
+                        tma_store_2d(&tmO, slot, n0, row0);
+                        bulk_commit();
+                    }
+                }
+                // ---- exact two-pass variance, then LayerNorm -> bf16 XN
+                const float mean = sum * inv_n;
+                float sq = 0.f;
+                for (int c = 0; c < nchunk; ++c) {
+                    float v[32];
+                    tmem_ld32(lane_taddr + c * 32, v);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const float d = v[i] - mean;
+                        sq += d * d;
+                    }
+                }
+                const float rstd = rsqrtf(sq * inv_n + p.ln_eps);
+                for (int c = 0; c < p.N / 64; ++c, ++ri) {
+                    uint8_t* slot = my_slots + (ri % ES) * G2_SLOT_BYTES;
+                    if (lane == 0) bulk_wait_read<1>();
+                    __syncwarp();
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        float v[32];
+                        const int n0 = c * 64 + 32 * h;
+                        tmem_ld32(lane_taddr + n0, v);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const float4 g0 = __ldg(reinterpret_cast<const float4*>(p.ln_g + n0 + 8 * j));
+                            const float4 g1 = __ldg(reinterpret_cast<const float4*>(p.ln_g + n0 + 8 * j + 4));
+                            const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.ln_b + n0 + 8 * j));
+                            const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.ln_b + n0 + 8 * j + 4));
+                            uint4 o;
+                            o.x = pack_bf16((v[8 * j] - mean) * rstd * g0.x + b0.x, (v[8 * j + 1] - mean) * rstd * g0.y + b0.y);
+                            o.y = pack_bf16((v[8 * j + 2] - mean) * rstd * g0.z + b0.z, (v[8 * j + 3] - mean) * rstd * g0.w + b0.w);
+                            o.z = pack_bf16((v[8 * j + 4] - mean) * rstd * g1.x + b1.x, (v[8 * j + 5] - mean) * rstd * g1.y + b1.y);
+                            o.w = pack_bf16((v[8 * j + 6] - mean) * rstd * g1.z + b1.z, (v[8 * j + 7] - mean) * rstd * g1.w + b1.w);
+                            *reinterpret_cast<uint4*>(slot + slot_off(lane, 4 * h + j)) = o;
+                        }
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0 && row0 < p.M) {
+                        tma_store_2d(&tmN, slot, c * 64, row0);
+                        bulk_commit();
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty_bar[0]);
+            }
+        }
+        if (lane == 0) bulk_wait_all();      // smem must outlive the last TMA stores
+        __syncwarp();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+}  // namespace ddc

@@ -117,13 +117,19 @@ int ddc_launches_per_step(const ddc_plan* plan);
 
 /* ---- kernel-level entry points (unit tests; hosts that schedule kernels themselves) ---- */
 
-/* out = epilogue(A' * W^T + bias).  amode 0: A is bf16 [m_pad, K]; amode 1: A is fp32
- * [m_pad, K] and A' = LayerNorm(A; ln_g, ln_b, eps 1e-5) (reference ViT.py:124,128,182).
- * epi 0: bf16 out; 1: bf16 gelu_erf out (ViT.py:85-86); 2: fp32 out += (residual, in place,
- * ViT.py:136-137); 3: fp32 out.  W: bf16 [N, K]; K % 64 == 0; N % 16 == 0; rows of A are
- * allocated up to a multiple of 128, only the first M rows of out are written. */
-int ddc_k_gemm(int32_t amode, int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const float* ln_g,
-               const float* ln_b, const void* W, const float* bias, void* out, int32_t ld_out, void* stream);
+/* Streaming GEMM, out = epilogue(A * W^T + bias).  A: bf16 [m_pad, K] (rows allocated up to
+ * a multiple of 128), W: bf16 [N, K], K % 64 == 0, ld_out == N.  epi 0: bf16 out (qkv,
+ * reference ViT.py:107); 1: bf16 gelu_erf out (fc1, ViT.py:85-86); 2: fp32 out (head,
+ * ViT.py:213).  N % 64 == 0 for epi 0/1, N % 16 == 0 for epi 2.  Only rows < M are written. */
+int ddc_k_gemm(int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const void* W, const float* bias, void* out,
+               int32_t ld_out, void* stream);
+
+/* Residual GEMM with the following LayerNorm fused in (proj / fc2, reference ViT.py:136-137
+ * then :133/:137/:212):  x[M, C] += A * W^T + bias  (fp32, in place; x allocated to m_pad
+ * rows), and xn[M, C] = bf16(LayerNorm(x_new; ln_g, ln_b, eps 1e-5)).  A: bf16 [m_pad, K],
+ * W: bf16 [C, K]; C % 64 == 0, C <= 512, K % 64 == 0. */
+int ddc_k_gemm_resid_ln(int32_t M, int32_t C, int32_t K, const void* A, const void* W, const float* bias, float* x,
+                        const float* ln_g, const float* ln_b, void* xn, void* stream);
 
 /* softmax(q k^T / sqrt(d)) v per (image, head) (reference ViT.py:107-114).
  * qkv: bf16 [B*L, 3C] (column s*C + head*d + e); out: bf16 [B*L, C]. */
