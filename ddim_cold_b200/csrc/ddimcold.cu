@@ -117,30 +117,58 @@ static int num_sms() {
     return sms[dev];
 }
 
-template <int EPI>
-static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR,
-                        const CUtensorMap& tmN, Gemm2Params p, cudaStream_t st) {
+template <int EPI, bool F16, int CS>
+static int launch_gemm2_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR,
+                             const CUtensorMap& tmN, const Gemm2Params& p, size_t smem, cudaStream_t st) {
     static int attr_dev_mask = 0;   // bit per device where the smem attribute has been raised
     int dev = 0;
     CK(cudaGetDevice(&dev));
+    auto kern = gemm2_kernel<EPI, F16, CS>;
     if (!(attr_dev_mask & (1 << dev))) {
-        CK(cudaFuncSetAttribute(gemm2_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_dev_mask |= (1 << dev);
     }
+    const int sms = num_sms();
+    int grid = p.num_tiles < sms ? p.num_tiles : sms;
+    grid = grid / CS * CS;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(G2_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CS;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmO, tmR, tmN, p));
+    return DDC_OK;
+}
+
+// W tiles are multicast to the `cs` CTAs of a cluster; tmB's box must hold bn/cs rows.
+static int gemm_cluster_size(int M) { return (M + G2_BM - 1) / G2_BM >= 2 ? 2 : 1; }
+
+template <int EPI>
+static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR,
+                        const CUtensorMap& tmN, Gemm2Params p, bool f16, int cs, cudaStream_t st) {
     constexpr bool rowblock = (EPI == R_RESID || EPI == R_EMBED);
     const bool bn_ok = (EPI == S_F32) ? (p.bn % 16 == 0) : (rowblock ? (p.bn % 32 == 0) : (p.bn % 64 == 0));
     if (p.K % G2_BK != 0 || p.K > 512 || !bn_ok || p.bn > 256 || p.bn <= 0 || p.N % p.bn != 0 || p.stages < 2 ||
-        p.stages > 8 || (rowblock && (p.N > 512 || p.N / p.bn > 4 || p.N % 64 != 0)))
-        return fail(DDC_E_INVALID, "gemm: unsupported M=%d N=%d K=%d bn=%d stages=%d epi=%d", p.M, p.N, p.K, p.bn,
-                    p.stages, EPI);
+        p.stages > 8 || (rowblock && (p.N > 512 || p.N / p.bn > 4 || p.N % 64 != 0)) || (cs != 1 && cs != 2) ||
+        (p.bn / cs) % 8 != 0)
+        return fail(DDC_E_INVALID, "gemm: unsupported M=%d N=%d K=%d bn=%d stages=%d epi=%d cs=%d", p.M, p.N, p.K, p.bn,
+                    p.stages, EPI, cs);
     const size_t smem = gemm2_smem_bytes(p.K, p.bn, p.stages, rowblock);
     if (smem > 227 * 1024) return fail(DDC_E_INVALID, "gemm: %zu B of shared memory needed", smem);
-    p.num_tiles = (p.M + G2_BM - 1) / G2_BM;
-    const int sms = num_sms();
-    const int grid = p.num_tiles < sms ? p.num_tiles : sms;
-    gemm2_kernel<EPI><<<grid, G2_THREADS, smem, st>>>(tmA, tmB, tmO, tmR, tmN, p);
-    CK(cudaGetLastError());
-    return DDC_OK;
+    p.num_tiles = ((p.M + G2_BM - 1) / G2_BM + cs - 1) / cs * cs;
+    if (f16) {
+        if (cs == 2) return launch_gemm2_inst<EPI, true, 2>(tmA, tmB, tmO, tmR, tmN, p, smem, st);
+        return launch_gemm2_inst<EPI, true, 1>(tmA, tmB, tmO, tmR, tmN, p, smem, st);
+    }
+    if (cs == 2) return launch_gemm2_inst<EPI, false, 2>(tmA, tmB, tmO, tmR, tmN, p, smem, st);
+    return launch_gemm2_inst<EPI, false, 1>(tmA, tmB, tmO, tmR, tmN, p, smem, st);
 }
 
 // ------------------------------------------------------------------------------- attention launch
@@ -154,31 +182,41 @@ static int att_pick_kc(int L) {
     return best;
 }
 
-template <int D, int KC>
+template <int D, int KC, bool F16>
 static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads, cudaStream_t st) {
     static int attr_dev_mask = 0;
     int dev = 0;
     CK(cudaGetDevice(&dev));
-    const size_t smem = att_smem_bytes(L, D, KC);
-    if (smem > 227 * 1024) return fail(DDC_E_INVALID, "attention: L=%d needs %zu B of shared memory", L, smem);
     if (!(attr_dev_mask & (1 << dev))) {
-        CK(cudaFuncSetAttribute(attention_kernel<D, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CK(cudaFuncSetAttribute(attention_head_kernel<D, KC, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CK(cudaFuncSetAttribute(attention_group_kernel<D, KC, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_dev_mask |= (1 << dev);
     }
-    int warps = (L + 15) / 16;
-    if (warps > ATT_MAX_WARPS) warps = ATT_MAX_WARPS;
     const float scale_log2e = (1.0f / sqrtf(static_cast<float>(D))) * 1.44269504088896340736f;
-    attention_kernel<D, KC><<<dim3(heads, B), warps * 32, smem, st>>>(qkv, out, L, C, scale_log2e);
+    const int qtiles = (L + 15) / 16;
+    constexpr int G = 128 / D;
+    const size_t gsmem = att_group_smem_bytes(L, D, KC, G);
+    if (heads % G == 0 && gsmem <= 100 * 1024) {      // >= 2 CTAs per SM: one image's head group per CTA
+        const int warps = qtiles < ATT_GROUP_WARPS ? qtiles : ATT_GROUP_WARPS;
+        attention_group_kernel<D, KC, F16><<<dim3(heads / G, B), warps * 32, gsmem, st>>>(qkv, out, L, C, scale_log2e);
+    } else {
+        const size_t smem = att_head_smem_bytes(L, D, KC);
+        if (smem > 227 * 1024) return fail(DDC_E_INVALID, "attention: L=%d needs %zu B of shared memory", L, smem);
+        const int warps = qtiles < ATT_MAX_WARPS ? qtiles : ATT_MAX_WARPS;
+        attention_head_kernel<D, KC, F16><<<dim3(heads, B), warps * 32, smem, st>>>(qkv, out, L, C, scale_log2e);
+    }
     CK(cudaGetLastError());
     return DDC_OK;
 }
 
-static int run_attention(const bf16* qkv, bf16* out, int B, int L, int C, int heads, cudaStream_t st) {
+static int run_attention(const bf16* qkv, bf16* out, int B, int L, int C, int heads, bool f16, cudaStream_t st) {
     if (heads <= 0 || C % heads != 0) return fail(DDC_E_INVALID, "attention: C=%d heads=%d", C, heads);
     const int D = C / heads;
     const int kc = att_pick_kc(L);
-#define ATT_CASE(DD, KK) \
-    if (D == DD && kc == KK) return launch_att<DD, KK>(qkv, out, B, L, C, heads, st);
+#define ATT_CASE(DD, KK)                                                                \
+    if (D == DD && kc == KK)                                                            \
+        return f16 ? launch_att<DD, KK, true>(qkv, out, B, L, C, heads, st)             \
+                   : launch_att<DD, KK, false>(qkv, out, B, L, C, heads, st);
     ATT_CASE(32, 128) ATT_CASE(32, 96) ATT_CASE(32, 80) ATT_CASE(32, 64) ATT_CASE(32, 48) ATT_CASE(32, 32)
     ATT_CASE(64, 128) ATT_CASE(64, 96) ATT_CASE(64, 80) ATT_CASE(64, 64) ATT_CASE(64, 48) ATT_CASE(64, 32)
 #undef ATT_CASE
@@ -189,7 +227,7 @@ static int run_attention(const bf16* qkv, bf16* out, int B, int L, int C, int he
 struct LayerW {
     float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *b_qkv, *b_proj, *b_fc1, *b_fc2;
     bf16 *w_qkv, *w_proj, *w_fc1, *w_fc2;
-    CUtensorMap tm_qkv, tm_proj, tm_fc1, tm_fc2;
+    CUtensorMap tm_qkv[2], tm_proj[2], tm_fc1[2], tm_fc2[2];   // W tile boxes for cluster size 1 and 2
 };
 
 struct GraphKey {
@@ -206,6 +244,7 @@ struct ddc_plan {
     int L, n, P, C, Kp, Mpad;
     int bn_qkv, bn_fc1, bn_row, bn_head;
     bool packed;
+    bool f16;       // 16-bit operand format: false = bfloat16 (default), true = IEEE half
     // weight arena
     bf16* w_patch;
     float* posb;
@@ -213,7 +252,7 @@ struct ddc_plan {
     std::vector<LayerW> layers;
     float *lnf_g, *lnf_b, *b_head;
     bf16* w_head;
-    CUtensorMap tm_wpatch, tm_whead;
+    CUtensorMap tm_wpatch[2], tm_whead[2];
     // work arena
     float* X;
     bf16 *QKV, *O, *Hd, *Ap, *XN;
@@ -336,6 +375,7 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
     derive(pl, shape, max_batch);
     pl->device = device;
     pl->packed = false;
+    pl->f16 = false;
     pl->gexec = nullptr;
     pl->gkey = GraphKey{0, nullptr, nullptr, nullptr, nullptr};
     size_t w = 0, k = 0;
@@ -355,13 +395,15 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
     mk(&pl->tm_Hd, false, pl->Hd, Mp, C, G2_BM);
     mk(&pl->tm_XN, false, pl->XN, Mp, C, G2_BM);
     mk(&pl->tm_Xld, true, pl->X, Mp, C, 32);
-    mk(&pl->tm_wpatch, false, pl->w_patch, C, pl->Kp, pl->bn_row);
-    mk(&pl->tm_whead, false, pl->w_head, pl->P, C, pl->bn_head);
-    for (auto& l : pl->layers) {
-        mk(&l.tm_qkv, false, l.w_qkv, 3 * C, C, pl->bn_qkv);
-        mk(&l.tm_proj, false, l.w_proj, C, C, pl->bn_row);
-        mk(&l.tm_fc1, false, l.w_fc1, C, C, pl->bn_fc1);
-        mk(&l.tm_fc2, false, l.w_fc2, C, C, pl->bn_row);
+    for (int cs = 1; cs <= 2; ++cs) {
+        mk(&pl->tm_wpatch[cs - 1], false, pl->w_patch, C, pl->Kp, pl->bn_row / cs);
+        mk(&pl->tm_whead[cs - 1], false, pl->w_head, pl->P, C, pl->bn_head / cs);
+        for (auto& l : pl->layers) {
+            mk(&l.tm_qkv[cs - 1], false, l.w_qkv, 3 * C, C, pl->bn_qkv / cs);
+            mk(&l.tm_proj[cs - 1], false, l.w_proj, C, C, pl->bn_row / cs);
+            mk(&l.tm_fc1[cs - 1], false, l.w_fc1, C, C, pl->bn_fc1 / cs);
+            mk(&l.tm_fc2[cs - 1], false, l.w_fc2, C, C, pl->bn_row / cs);
+        }
     }
     if (r != DDC_OK) {
         delete pl;
@@ -375,6 +417,20 @@ extern "C" int ddc_plan_destroy(ddc_plan* plan) {
     if (plan == nullptr) return DDC_OK;
     if (plan->gexec) cudaGraphExecDestroy(plan->gexec);
     delete plan;
+    return DDC_OK;
+}
+
+extern "C" int ddc_plan_set_operand_format(ddc_plan* plan, int32_t fmt) {
+    if (plan == nullptr) return fail(DDC_E_INVALID, "plan is NULL");
+    if (fmt != 0 && fmt != 1) return fail(DDC_E_INVALID, "operand format %d (0 = bf16, 1 = fp16)", fmt);
+    if (plan->f16 != (fmt == 1)) {
+        plan->f16 = (fmt == 1);
+        plan->packed = false;            // packed weights are in the old format
+        if (plan->gexec) {
+            cudaGraphExecDestroy(plan->gexec);
+            plan->gexec = nullptr;
+        }
+    }
     return DDC_OK;
 }
 
@@ -394,7 +450,8 @@ extern "C" int ddc_pack_weights(ddc_plan* pl, const float* const* t, int32_t n_t
     CK(cudaSetDevice(pl->device));
     const int C = pl->C, L = pl->L, P = pl->P;
     auto pack = [&](const float* src, bf16* dst, int rows, int cols, int cols_pad) {
-        pack_bf16_kernel<<<296, 256, 0, st>>>(src, dst, rows, cols, cols_pad);
+        if (pl->f16) pack_16bit_kernel<true><<<296, 256, 0, st>>>(src, dst, rows, cols, cols_pad);
+        else pack_16bit_kernel<false><<<296, 256, 0, st>>>(src, dst, rows, cols, cols_pad);
     };
     auto copy = [&](const float* src, float* dst, size_t n) { copy_f32_kernel<<<148, 256, 0, st>>>(src, dst, n); };
     const float* cls = t[0];
@@ -479,8 +536,14 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     const ddc_shape& s = pl->sh;
     const int C = pl->C, L = pl->L, M = B * L;
     TRY(ensure_store_maps(pl, B));
-    patchify_kernel<<<dim3(s.img_h / s.patch, B), 256, 0, st>>>(x, pl->Ap, s.img_h, s.img_w, s.patch, L, pl->Kp,
-                                                                  use_step_ctr ? pl->ctr : nullptr);
+    const bool f16 = pl->f16;
+    const int cs = gemm_cluster_size(M);
+    if (f16)
+        patchify_kernel<true><<<dim3(s.img_h / s.patch, B), 256, 0, st>>>(x, pl->Ap, s.img_h, s.img_w, s.patch, L,
+                                                                            pl->Kp, use_step_ctr ? pl->ctr : nullptr);
+    else
+        patchify_kernel<false><<<dim3(s.img_h / s.patch, B), 256, 0, st>>>(x, pl->Ap, s.img_h, s.img_w, s.patch, L,
+                                                                             pl->Kp, use_step_ctr ? pl->ctr : nullptr);
     CK(cudaGetLastError());
     MARK(KC_PATCHIFY);
     const LayerW& l0 = pl->layers[0];
@@ -488,37 +551,37 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     g.M = M; g.N = C; g.K = pl->Kp; g.bn = pl->bn_row; g.stages = pick_stages2(g.K, g.bn, true);
     g.ln_g = l0.ln1_g; g.ln_b = l0.ln1_b; g.ln_eps = 1e-5f;
     g.posb = pl->posb; g.L = L; g.time_tab = pl->time_tab; g.t_img = t_img; g.tbl = pl->tbl; g.cur = pl->ctr; g.B = B;
-    TRY((launch_gemm2<R_EMBED>(pl->tm_Ap, pl->tm_wpatch, pl->st_X, pl->tm_Xld, pl->st_XN, g, st)));
+    TRY((launch_gemm2<R_EMBED>(pl->tm_Ap, pl->tm_wpatch[cs - 1], pl->st_X, pl->tm_Xld, pl->st_XN, g, f16, cs, st)));
     MARK(KC_EMBED);
     for (int i = 0; i < s.depth; ++i) {
         LayerW& l = pl->layers[i];
         Gemm2Params q{};
         q.M = M; q.N = 3 * C; q.K = C; q.bn = pl->bn_qkv; q.stages = pick_stages2(q.K, q.bn, false);
         q.bias = l.b_qkv;
-        TRY((launch_gemm2<S_BF16>(pl->tm_XN, l.tm_qkv, pl->st_QKV, pl->tm_Xld, pl->st_XN, q, st)));
+        TRY((launch_gemm2<S_BF16>(pl->tm_XN, l.tm_qkv[cs - 1], pl->st_QKV, pl->tm_Xld, pl->st_XN, q, f16, cs, st)));
         MARK(KC_QKV);
-        TRY(run_attention(pl->QKV, pl->O, B, L, C, s.heads, st));
+        TRY(run_attention(pl->QKV, pl->O, B, L, C, s.heads, f16, st));
         MARK(KC_ATTN);
         Gemm2Params r{};
         r.M = M; r.N = C; r.K = C; r.bn = pl->bn_row; r.stages = pick_stages2(r.K, r.bn, true);
         r.bias = l.b_proj; r.ln_g = l.ln2_g; r.ln_b = l.ln2_b; r.ln_eps = 1e-5f;
-        TRY((launch_gemm2<R_RESID>(pl->tm_O, l.tm_proj, pl->st_X, pl->tm_Xld, pl->st_XN, r, st)));
+        TRY((launch_gemm2<R_RESID>(pl->tm_O, l.tm_proj[cs - 1], pl->st_X, pl->tm_Xld, pl->st_XN, r, f16, cs, st)));
         MARK(KC_PROJ);
         Gemm2Params f{};
         f.M = M; f.N = C; f.K = C; f.bn = pl->bn_fc1; f.stages = pick_stages2(f.K, f.bn, false);
         f.bias = l.b_fc1;
-        TRY((launch_gemm2<S_BF16_GELU>(pl->tm_XN, l.tm_fc1, pl->st_Hd, pl->tm_Xld, pl->st_XN, f, st)));
+        TRY((launch_gemm2<S_BF16_GELU>(pl->tm_XN, l.tm_fc1[cs - 1], pl->st_Hd, pl->tm_Xld, pl->st_XN, f, f16, cs, st)));
         MARK(KC_FC1);
         r.bias = l.b_fc2;
         r.ln_g = (i + 1 < s.depth) ? pl->layers[i + 1].ln1_g : pl->lnf_g;
         r.ln_b = (i + 1 < s.depth) ? pl->layers[i + 1].ln1_b : pl->lnf_b;
-        TRY((launch_gemm2<R_RESID>(pl->tm_Hd, l.tm_fc2, pl->st_X, pl->tm_Xld, pl->st_XN, r, st)));
+        TRY((launch_gemm2<R_RESID>(pl->tm_Hd, l.tm_fc2[cs - 1], pl->st_X, pl->tm_Xld, pl->st_XN, r, f16, cs, st)));
         MARK(KC_FC2);
     }
     Gemm2Params h{};
     h.M = M; h.N = pl->P; h.K = C; h.bn = pl->bn_head; h.stages = pick_stages2(h.K, h.bn, false);
     h.bias = pl->b_head; h.out_f32 = pl->Y; h.ld_f32 = pl->P;
-    TRY((launch_gemm2<S_F32>(pl->tm_XN, pl->tm_whead, pl->st_XN, pl->tm_Xld, pl->st_XN, h, st)));
+    TRY((launch_gemm2<S_F32>(pl->tm_XN, pl->tm_whead[cs - 1], pl->st_XN, pl->tm_Xld, pl->st_XN, h, f16, cs, st)));
     MARK(KC_HEAD);
     return DDC_OK;
 }
@@ -690,8 +753,10 @@ extern "C" int ddc_cold_table(ddc_step* tab, int32_t capacity, int32_t* n_steps)
 }
 
 // ------------------------------------------------------------------------------- kernel-level entries
-extern "C" int ddc_k_gemm(int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const void* W, const float* bias,
-                          void* out, int32_t ld_out, void* stream) {
+extern "C" int ddc_k_gemm(int32_t fmt, int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const void* W,
+                          const float* bias, void* out, int32_t ld_out, void* stream) {
+    const bool f16 = fmt == 1;
+    const int cs = gemm_cluster_size(M);
     if (A == nullptr || W == nullptr || bias == nullptr || out == nullptr) return fail(DDC_E_INVALID, "NULL tensor");
     if (M <= 0 || N <= 0 || K <= 0 || K % 64 != 0 || ld_out != N) return fail(DDC_E_INVALID, "bad sizes");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -700,24 +765,24 @@ extern "C" int ddc_k_gemm(int32_t epi, int32_t M, int32_t N, int32_t K, const vo
     if (bn == 0) return fail(DDC_E_INVALID, "N=%d must be a multiple of %d", N, epi == S_F32 ? 16 : 64);
     CUtensorMap tmA, tmB, tmO;
     TRY(make_tmap(&tmA, false, A, Mp, K, G2_BM));
-    TRY(make_tmap(&tmB, false, W, N, K, bn));
+    TRY(make_tmap(&tmB, false, W, N, K, bn / cs));
     Gemm2Params p{};
     p.M = M; p.N = N; p.K = K; p.bn = bn; p.stages = pick_stages2(K, bn, false); p.bias = bias;
     switch (epi) {
         case S_BF16:
             TRY(make_tmap(&tmO, false, out, M, N, 32));
-            return launch_gemm2<S_BF16>(tmA, tmB, tmO, tmA, tmA, p, st);
+            return launch_gemm2<S_BF16>(tmA, tmB, tmO, tmA, tmA, p, f16, cs, st);
         case S_BF16_GELU:
             TRY(make_tmap(&tmO, false, out, M, N, 32));
-            return launch_gemm2<S_BF16_GELU>(tmA, tmB, tmO, tmA, tmA, p, st);
+            return launch_gemm2<S_BF16_GELU>(tmA, tmB, tmO, tmA, tmA, p, f16, cs, st);
         case S_F32:
             p.out_f32 = static_cast<float*>(out); p.ld_f32 = ld_out;
-            return launch_gemm2<S_F32>(tmA, tmB, tmA, tmA, tmA, p, st);
+            return launch_gemm2<S_F32>(tmA, tmB, tmA, tmA, tmA, p, f16, cs, st);
     }
     return fail(DDC_E_INVALID, "epi=%d", epi);
 }
 
-extern "C" int ddc_k_gemm_resid_ln(int32_t M, int32_t C, int32_t K, const void* A, const void* W, const float* bias,
+extern "C" int ddc_k_gemm_resid_ln(int32_t fmt, int32_t M, int32_t C, int32_t K, const void* A, const void* W, const float* bias,
                                    float* x, const float* ln_g, const float* ln_b, void* xn, void* stream) {
     if (A == nullptr || W == nullptr || bias == nullptr || x == nullptr || ln_g == nullptr || ln_b == nullptr ||
         xn == nullptr)
@@ -728,31 +793,36 @@ extern "C" int ddc_k_gemm_resid_ln(int32_t M, int32_t C, int32_t K, const void* 
     const int bn = pick_bn_row(C);
     CUtensorMap tmA, tmB, tmO, tmR, tmN;
     TRY(make_tmap(&tmA, false, A, Mp, K, G2_BM));
-    TRY(make_tmap(&tmB, false, W, C, K, bn));
+    const int cs = gemm_cluster_size(M);
+    TRY(make_tmap(&tmB, false, W, C, K, bn / cs));
     TRY(make_tmap(&tmO, true, x, M, C, 32));
     TRY(make_tmap(&tmR, true, x, Mp, C, 32));
     TRY(make_tmap(&tmN, false, xn, M, C, 32));
     Gemm2Params p{};
     p.M = M; p.N = C; p.K = K; p.bn = bn; p.stages = pick_stages2(K, bn, true); p.bias = bias;
     p.ln_g = ln_g; p.ln_b = ln_b; p.ln_eps = 1e-5f;
-    return launch_gemm2<R_RESID>(tmA, tmB, tmO, tmR, tmN, p, st);
+    return launch_gemm2<R_RESID>(tmA, tmB, tmO, tmR, tmN, p, fmt == 1, cs, st);
 }
 
-extern "C" int ddc_k_attention(const void* qkv, void* out, int32_t batch, int32_t L, int32_t C, int32_t heads,
-                               void* stream) {
+extern "C" int ddc_k_attention(int32_t fmt, const void* qkv, void* out, int32_t batch, int32_t L, int32_t C,
+                               int32_t heads, void* stream) {
     if (qkv == nullptr || out == nullptr || batch <= 0 || L <= 0) return fail(DDC_E_INVALID, "bad argument");
-    return run_attention(static_cast<const bf16*>(qkv), static_cast<bf16*>(out), batch, L, C, heads,
+    return run_attention(static_cast<const bf16*>(qkv), static_cast<bf16*>(out), batch, L, C, heads, fmt == 1,
                          static_cast<cudaStream_t>(stream));
 }
 
-extern "C" int ddc_k_patchify(const float* x, void* ap, int32_t batch, int32_t H, int32_t W, int32_t patch, int32_t Kp,
+extern "C" int ddc_k_patchify(int32_t fmt, const float* x, void* ap, int32_t batch, int32_t H, int32_t W, int32_t patch, int32_t Kp,
                               void* stream) {
     if (x == nullptr || ap == nullptr || batch <= 0 || patch <= 0 || patch % 2 || H % patch || W % patch ||
         Kp < 3 * patch * patch || Kp % 2)
         return fail(DDC_E_INVALID, "bad argument");
     const int L = (H / patch) * (W / patch) + 1;
-    patchify_kernel<<<dim3(H / patch, batch), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        x, static_cast<bf16*>(ap), H, W, patch, L, Kp, nullptr);
+    if (fmt == 1)
+        patchify_kernel<true><<<dim3(H / patch, batch), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+            x, static_cast<bf16*>(ap), H, W, patch, L, Kp, nullptr);
+    else
+        patchify_kernel<false><<<dim3(H / patch, batch), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+            x, static_cast<bf16*>(ap), H, W, patch, L, Kp, nullptr);
     CK(cudaGetLastError());
     return DDC_OK;
 }

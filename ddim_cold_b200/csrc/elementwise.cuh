@@ -13,6 +13,7 @@ namespace ddc {
 // [3p^2, Kp) are zero padding up to the 64-element K block.
 // grid (Hp, B).  Block (0,0) thread 0 also advances the device-side step counter that every
 // later kernel of the step reads: cur <- next, next <- next + 1.
+template <bool F16>
 __global__ void __launch_bounds__(256)
 patchify_kernel(const float* __restrict__ x, bf16* __restrict__ ap, int H, int W, int p, int L, int Kp,
                 int* step_ctr) {
@@ -39,7 +40,7 @@ patchify_kernel(const float* __restrict__ x, bf16* __restrict__ ap, int H, int W
             v0 = v.x;
             v1 = v.y;
         }
-        *reinterpret_cast<uint32_t*>(ap + (row0 + pw) * Kp + kc) = pack_bf16(v0, v1);
+        *reinterpret_cast<uint32_t*>(ap + (row0 + pw) * Kp + kc) = pack2<F16>(v0, v1);
     }
     if (ph == 0) {
         for (int i = threadIdx.x; i < half; i += blockDim.x)
@@ -119,14 +120,16 @@ __global__ void __launch_bounds__(256) head_ddim_kernel(const HeadDdimParams q) 
 }
 
 // ---------------------------------------------------------------------------- weight packing (one-off)
-// fp32 [rows, cols] -> bf16 [rows, cols_pad], zero padded
-__global__ void pack_bf16_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int rows, int cols,
-                                 int cols_pad) {
+// fp32 [rows, cols] -> 16-bit operand format [rows, cols_pad], zero padded
+template <bool F16>
+__global__ void pack_16bit_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int rows, int cols,
+                                  int cols_pad) {
     const size_t n = static_cast<size_t>(rows) * cols_pad;
     for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
          i += static_cast<size_t>(gridDim.x) * blockDim.x) {
         const int r = static_cast<int>(i / cols_pad), c = static_cast<int>(i - static_cast<size_t>(r) * cols_pad);
-        dst[i] = __float2bfloat16_rn(c < cols ? src[static_cast<size_t>(r) * cols + c] : 0.f);
+        const float v = c < cols ? src[static_cast<size_t>(r) * cols + c] : 0.f;
+        reinterpret_cast<uint16_t*>(dst)[i] = static_cast<uint16_t>(pack2<F16>(v, 0.f) & 0xFFFFu);
     }
 }
 

@@ -69,7 +69,7 @@ inline size_t gemm2_smem_bytes(int K, int bn, int stages, bool rowblock) {
 // byte offset of 16-byte chunk `j` of row `r` inside a 128-byte-swizzled 32-row slot
 __device__ __forceinline__ uint32_t slot_off(int r, int j) { return r * 128 + ((j ^ (r & 7)) << 4); }
 
-template <int EPI>
+template <int EPI, bool F16, int CS>
 __global__ void __launch_bounds__(G2_THREADS, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR,
@@ -98,6 +98,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    // CTAs of a cluster take adjacent M tiles and share every W tile through TMA multicast; p.num_tiles is a
+    // multiple of CS, so all CTAs of a cluster run the same number of iterations (surplus tiles store nothing).
+    const uint32_t crank = CS > 1 ? cluster_ctarank() : 0u;
+    const int first_tile = static_cast<int>((blockIdx.x / CS) * CS + crank);
+    const int tile_step = gridDim.x;
+    constexpr uint16_t kMask = static_cast<uint16_t>((1u << CS) - 1u);
     const uint32_t acc_stride = g2_pow2_cols(p.bn);
     const uint32_t tmem_cols = ROWBLOCK ? g2_pow2_cols(p.N) : g2_pow2_cols(2 * acc_stride);
 
@@ -109,7 +115,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (ROWBLOCK) tma_prefetch_desc(&tmN);
         for (int i = 0; i < 8; ++i) {
             mbar_init(&full_bar[i], 1);
-            mbar_init(&empty_bar[i], 1);
+            mbar_init(&empty_bar[i], CS);        // every CTA of the cluster must have consumed the stage
             mbar_init(&afull_bar[i], 1);
             mbar_init(&aempty_bar[i], 1);
         }
@@ -125,6 +131,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
     tc_fence_before();
     __syncthreads();
+    if (CS > 1) cluster_sync_all();              // peers' barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -132,7 +139,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         // ================================================================= TMA producer
         if (lane == 0) {
             uint32_t stage = 0, phase = 0, tcount = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+            for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
                 const int m0 = tile * G2_BM;
                 for (int kb = 0; kb < kblocks; ++kb) {
                     mbar_wait(&aempty_bar[kb], (tcount & 1) ^ 1);
@@ -143,8 +150,15 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     for (int kb = 0; kb < kblocks; ++kb) {
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         mbar_arrive_expect_tx(&full_bar[stage], b_stage_bytes);
-                        tma_load_2d(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
-                                    kb * G2_BK, nt * p.bn);
+                        if (CS == 1) {
+                            tma_load_2d(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
+                                        kb * G2_BK, nt * p.bn);
+                        } else {      // this CTA fetches rows [crank*bn/CS, +bn/CS) of the W tile for the whole cluster
+                            const uint32_t slice = b_stage_bytes / CS;
+                            tma_load_2d_mcast(smem_b + static_cast<size_t>(stage) * b_stage_bytes + crank * slice, &tmB,
+                                              &full_bar[stage], kb * G2_BK, nt * p.bn + static_cast<int>(crank) * (p.bn / CS),
+                                              kMask);
+                        }
                         if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -153,11 +167,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         __syncwarp();
     } else if (warp == 1) {
         // ================================================================= MMA issuer
-        const uint32_t idesc = umma_idesc_bf16(G2_BM, static_cast<uint32_t>(p.bn));
+        const uint32_t idesc = umma_idesc_16bit(G2_BM, static_cast<uint32_t>(p.bn), F16);
         const uint32_t a_base = smem_u32(smem_a);
         const uint32_t b_base = smem_u32(smem_b);
         uint32_t stage = 0, phase = 0, tcount = 0, acc_it = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+        for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
             for (int nt = 0; nt < num_nt; ++nt) {
                 uint32_t d_tmem;
                 uint64_t* done_bar;
@@ -184,7 +198,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                             const uint64_t bd = umma_desc_sw128(b_base + stage * b_stage_bytes + k * 32);
                             umma_bf16_ss(d_tmem, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
                         }
-                        umma_commit(&empty_bar[stage]);
+                        if (CS == 1) umma_commit(&empty_bar[stage]);
+                        else umma_commit_mcast(&empty_bar[stage], kMask);
                         if (nt == num_nt - 1) umma_commit(&aempty_bar[kb]);
                         if (kb == kblocks - 1) umma_commit(done_bar);
                     }
@@ -201,7 +216,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         uint32_t tcount = 0;
         if (!ROWBLOCK) {
             uint32_t acc_it = 0, slot_it = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+            for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
                 const int row0 = tile * G2_BM + q * 32;
                 const int row = row0 + lane;
                 for (int nt = 0; nt < num_nt; ++nt, ++acc_it) {
@@ -246,10 +261,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 #pragma unroll
                                 for (int j = 0; j < 4; ++j) {
                                     uint4 o;
-                                    o.x = pack_bf16(v[8 * j], v[8 * j + 1]);
-                                    o.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
-                                    o.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]);
-                                    o.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+                                    o.x = pack2<F16>(v[8 * j], v[8 * j + 1]);
+                                    o.y = pack2<F16>(v[8 * j + 2], v[8 * j + 3]);
+                                    o.z = pack2<F16>(v[8 * j + 4], v[8 * j + 5]);
+                                    o.w = pack2<F16>(v[8 * j + 6], v[8 * j + 7]);
                                     *reinterpret_cast<uint4*>(slot + slot_off(lane, 4 * h + j)) = o;
                                 }
                             }
@@ -272,7 +287,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             const float inv_n = 1.0f / static_cast<float>(p.N);
             uint32_t ri = 0;                        // residual / staging slot counter (this warp)
             uint32_t loads = 0;                     // residual loads issued so far (lane 0 bookkeeping = all lanes)
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+            for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
                 const int row0 = tile * G2_BM + q * 32;
                 const int row = row0 + lane;
                 const float* embed_pos = nullptr;
@@ -381,10 +396,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                             const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.ln_b + n0 + 8 * j));
                             const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.ln_b + n0 + 8 * j + 4));
                             uint4 o;
-                            o.x = pack_bf16((v[8 * j] - mean) * rstd * g0.x + b0.x, (v[8 * j + 1] - mean) * rstd * g0.y + b0.y);
-                            o.y = pack_bf16((v[8 * j + 2] - mean) * rstd * g0.z + b0.z, (v[8 * j + 3] - mean) * rstd * g0.w + b0.w);
-                            o.z = pack_bf16((v[8 * j + 4] - mean) * rstd * g1.x + b1.x, (v[8 * j + 5] - mean) * rstd * g1.y + b1.y);
-                            o.w = pack_bf16((v[8 * j + 6] - mean) * rstd * g1.z + b1.z, (v[8 * j + 7] - mean) * rstd * g1.w + b1.w);
+                            o.x = pack2<F16>((v[8 * j] - mean) * rstd * g0.x + b0.x, (v[8 * j + 1] - mean) * rstd * g0.y + b0.y);
+                            o.y = pack2<F16>((v[8 * j + 2] - mean) * rstd * g0.z + b0.z, (v[8 * j + 3] - mean) * rstd * g0.w + b0.w);
+                            o.z = pack2<F16>((v[8 * j + 4] - mean) * rstd * g1.x + b1.x, (v[8 * j + 5] - mean) * rstd * g1.y + b1.y);
+                            o.w = pack2<F16>((v[8 * j + 6] - mean) * rstd * g1.z + b1.z, (v[8 * j + 7] - mean) * rstd * g1.w + b1.w);
                             *reinterpret_cast<uint4*>(slot + slot_off(lane, 4 * h + j)) = o;
                         }
                     }
@@ -406,6 +421,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
     tc_fence_before();
     __syncthreads();
+    if (CS > 1) cluster_sync_all();              // no CTA leaves while a peer may still write its smem / barriers
     if (warp == 2) tmem_dealloc(tmem_base, tmem_cols);
 }
 

@@ -79,6 +79,12 @@ int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_t device, v
                     void* work_arena, size_t work_bytes, ddc_plan** out);
 int ddc_plan_destroy(ddc_plan* plan);
 
+/* Choose the 16-bit format of every tensor-core operand (weights and activations): 0 =
+ * bfloat16 (default), 1 = IEEE half.  Both run at the same tensor-core rate with fp32
+ * accumulation; half carries three more mantissa bits (the reference itself computes in fp32,
+ * ViT.py has no autocast on this path).  Must be followed by ddc_pack_weights. */
+int ddc_plan_set_operand_format(ddc_plan* plan, int32_t fmt);
+
 /* Pack an fp32 state dict into the plan's weight arena (bf16 K-major GEMM operands, folded
  * cls/pos/conv-bias rows, fp32 time table).  `tensors` is a HOST array of `n_tensors` device
  * pointers in the reference's state_dict order: cls_token, pos_embed, patch_embed.proj.weight,
@@ -115,29 +121,30 @@ int ddc_profile_steps(ddc_plan* plan, float* x, int32_t batch, const ddc_step* h
 /* Number of kernel launches one ddc_forward / one step of ddc_sample issues. */
 int ddc_launches_per_step(const ddc_plan* plan);
 
-/* ---- kernel-level entry points (unit tests; hosts that schedule kernels themselves) ---- */
+/* ---- kernel-level entry points (unit tests; hosts that schedule kernels themselves) ----
+ * `fmt` is the 16-bit operand format: 0 = bf16, 1 = fp16. */
 
 /* Streaming GEMM, out = epilogue(A * W^T + bias).  A: bf16 [m_pad, K] (rows allocated up to
  * a multiple of 128), W: bf16 [N, K], K % 64 == 0, ld_out == N.  epi 0: bf16 out (qkv,
  * reference ViT.py:107); 1: bf16 gelu_erf out (fc1, ViT.py:85-86); 2: fp32 out (head,
  * ViT.py:213).  N % 64 == 0 for epi 0/1, N % 16 == 0 for epi 2.  Only rows < M are written. */
-int ddc_k_gemm(int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const void* W, const float* bias, void* out,
+int ddc_k_gemm(int32_t fmt, int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const void* W, const float* bias, void* out,
                int32_t ld_out, void* stream);
 
 /* Residual GEMM with the following LayerNorm fused in (proj / fc2, reference ViT.py:136-137
  * then :133/:137/:212):  x[M, C] += A * W^T + bias  (fp32, in place; x allocated to m_pad
  * rows), and xn[M, C] = bf16(LayerNorm(x_new; ln_g, ln_b, eps 1e-5)).  A: bf16 [m_pad, K],
  * W: bf16 [C, K]; C % 64 == 0, C <= 512, K % 64 == 0. */
-int ddc_k_gemm_resid_ln(int32_t M, int32_t C, int32_t K, const void* A, const void* W, const float* bias, float* x,
+int ddc_k_gemm_resid_ln(int32_t fmt, int32_t M, int32_t C, int32_t K, const void* A, const void* W, const float* bias, float* x,
                         const float* ln_g, const float* ln_b, void* xn, void* stream);
 
 /* softmax(q k^T / sqrt(d)) v per (image, head) (reference ViT.py:107-114).
  * qkv: bf16 [B*L, 3C] (column s*C + head*d + e); out: bf16 [B*L, C]. */
-int ddc_k_attention(const void* qkv, void* out, int32_t batch, int32_t L, int32_t C, int32_t heads, void* stream);
+int ddc_k_attention(int32_t fmt, const void* qkv, void* out, int32_t batch, int32_t L, int32_t C, int32_t heads, void* stream);
 
 /* Patchify (im2col of the stride-p conv, reference ViT.py:150,154): x fp32 [B,3,H,W] ->
  * ap bf16 [B*L, Kp] with a zero cls row per image and zero K padding. */
-int ddc_k_patchify(const float* x, void* ap, int32_t batch, int32_t H, int32_t W, int32_t patch, int32_t Kp,
+int ddc_k_patchify(int32_t fmt, const float* x, void* ap, int32_t batch, int32_t H, int32_t W, int32_t patch, int32_t Kp,
                    void* stream);
 
 /* Unpatchify + clamp + DDIM update (reference ViT.py:214-217,229,233-234) for one step given

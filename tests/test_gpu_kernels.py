@@ -39,23 +39,29 @@ GEMM_SHAPES = [(200, 128, 64), (130, 192, 384), (1000, 1152, 384), (257 * 3, 768
                (128, 64, 64), (4097, 384, 384), (66560 // 4, 1152, 384), (40000, 256, 256)]
 
 
+def _op(t, fmt):
+    """Round to the 16-bit operand format; fp16 tensors travel as raw 16-bit words."""
+    return t.to(torch.float16 if fmt else torch.bfloat16)
+
+
 @pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
 @pytest.mark.parametrize("epi", [0, 1, 2])
-def test_gemm_stream(lib, M, N, K, epi):
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_gemm_stream(lib, M, N, K, epi, fmt):
     """qkv / fc1 / head GEMMs: persistent tcgen05 kernel, TMA in, TMA-store (bf16) or direct (fp32) out."""
     g = torch.Generator(device="cuda").manual_seed(M * 7 + N * 3 + K + epi)
     dev = "cuda"
-    W = (torch.randn(N, K, device=dev, generator=g) * 0.05).to(torch.bfloat16)
+    W = _op(torch.randn(N, K, device=dev, generator=g) * 0.05, fmt)
     bias = torch.randn(N, device=dev, generator=g) * 0.1
-    A = _pad_rows(torch.randn(M, K, device=dev, generator=g).to(torch.bfloat16))
+    A = _pad_rows(_op(torch.randn(M, K, device=dev, generator=g), fmt))
     ref = A[:M].float() @ W.float().T + bias
     if epi == 1:
         ref = torch.nn.functional.gelu(ref)
-    out = torch.full((M + 3, N), 7.0, device=dev, dtype=torch.float32 if epi == 2 else torch.bfloat16)
+    out = torch.full((M + 3, N), 7.0, device=dev, dtype=torch.float32 if epi == 2 else W.dtype)
     before = out.clone()
-    _check(lib.ddc_k_gemm(epi, M, N, K, A.data_ptr(), W.data_ptr(), bias.data_ptr(), out.data_ptr(), N, _stream()))
+    _check(lib.ddc_k_gemm(fmt, epi, M, N, K, A.data_ptr(), W.data_ptr(), bias.data_ptr(), out.data_ptr(), N, _stream()))
     torch.cuda.synchronize()
-    tol = 3e-3 if epi == 2 else 2e-2          # fp32 output vs bf16 output rounding
+    tol = 3e-3 if epi == 2 else (4e-3 if fmt else 2e-2)          # fp32 output vs 16-bit output rounding
     err = (out[:M].float() - ref).abs().max().item()
     assert err < tol * max(1.0, ref.abs().max().item()), (err, ref.abs().max().item())
     assert torch.equal(out[M:], before[M:]), "rows beyond M were written"
@@ -63,38 +69,41 @@ def test_gemm_stream(lib, M, N, K, epi):
 
 @pytest.mark.parametrize("M,C,K", [(200, 64, 64), (130, 384, 384), (1000, 256, 256), (4097, 384, 384), (300, 128, 192),
                                    (66560 // 2, 384, 384), (515, 512, 512)])
-def test_gemm_resid_layernorm(lib, M, C, K):
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_gemm_resid_layernorm(lib, M, C, K, fmt):
     """proj / fc2: x += A W^T + b in place (fp32) and the fused LayerNorm of the new row -> bf16."""
     g = torch.Generator(device="cuda").manual_seed(M + C + K)
     dev = "cuda"
-    W = (torch.randn(C, K, device=dev, generator=g) * 0.05).to(torch.bfloat16)
+    W = _op(torch.randn(C, K, device=dev, generator=g) * 0.05, fmt)
     bias = torch.randn(C, device=dev, generator=g) * 0.1
-    A = _pad_rows(torch.randn(M, K, device=dev, generator=g).to(torch.bfloat16))
+    A = _pad_rows(_op(torch.randn(M, K, device=dev, generator=g), fmt))
     x = _pad_rows(torch.randn(M, C, device=dev, generator=g) * 1.3 + 0.2)
     x[M:] = 5.0
     ln_g = 1 + 0.1 * torch.randn(C, device=dev, generator=g)
     ln_b = 0.1 * torch.randn(C, device=dev, generator=g)
-    xn = torch.full((M + 5, C), 3.0, device=dev, dtype=torch.bfloat16)
+    xn = torch.full((M + 5, C), 3.0, device=dev, dtype=W.dtype)
     x_ref = x[:M] + A[:M].float() @ W.float().T + bias
     xn_ref = torch.nn.functional.layer_norm(x_ref, (C,), ln_g, ln_b, 1e-5)
-    _check(lib.ddc_k_gemm_resid_ln(M, C, K, A.data_ptr(), W.data_ptr(), bias.data_ptr(), x.data_ptr(), ln_g.data_ptr(),
+    _check(lib.ddc_k_gemm_resid_ln(fmt, M, C, K, A.data_ptr(), W.data_ptr(), bias.data_ptr(), x.data_ptr(), ln_g.data_ptr(),
                                    ln_b.data_ptr(), xn.data_ptr(), _stream()))
     torch.cuda.synchronize()
     assert (x[:M] - x_ref).abs().max().item() < 3e-3 * max(1.0, x_ref.abs().max().item())
-    assert (xn[:M].float() - xn_ref).abs().max().item() < 2e-2 * max(1.0, xn_ref.abs().max().item())
+    assert (xn[:M].float() - xn_ref).abs().max().item() < (4e-3 if fmt else 2e-2) * max(1.0, xn_ref.abs().max().item())
     assert bool((x[M:] == 5.0).all()) and bool((xn[M:].float() == 3.0).all()), "rows beyond M were written"
 
 
-ATT_SHAPES = [(3, 65, 384, 12), (2, 257, 256, 4), (1, 626, 384, 12), (5, 17, 64, 2), (2, 33, 128, 2), (4, 16, 64, 1)]
+ATT_SHAPES = [(3, 65, 384, 12), (2, 257, 256, 4), (1, 626, 384, 12), (5, 17, 64, 2), (2, 33, 128, 2), (4, 16, 64, 1),
+              (300, 65, 384, 12), (3, 65, 128, 4), (2, 100, 256, 8), (2, 65, 256, 4)]
 
 
 @pytest.mark.parametrize("B,L,Cdim,heads", ATT_SHAPES)
-def test_attention(lib, B, L, Cdim, heads):
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_attention(lib, B, L, Cdim, heads, fmt):
     g = torch.Generator(device="cuda").manual_seed(L + heads)
     d = Cdim // heads
-    qkv = (torch.randn(B * L, 3 * Cdim, device="cuda", generator=g) * 1.5).to(torch.bfloat16)
-    out = torch.zeros(B * L, Cdim, device="cuda", dtype=torch.bfloat16)
-    _check(lib.ddc_k_attention(qkv.data_ptr(), out.data_ptr(), B, L, Cdim, heads, _stream()))
+    qkv = _op(torch.randn(B * L, 3 * Cdim, device="cuda", generator=g) * 1.5, fmt)
+    out = torch.zeros(B * L, Cdim, device="cuda", dtype=qkv.dtype)
+    _check(lib.ddc_k_attention(fmt, qkv.data_ptr(), out.data_ptr(), B, L, Cdim, heads, _stream()))
     torch.cuda.synchronize()
     x = qkv.float().reshape(B, L, 3, heads, d).permute(2, 0, 3, 1, 4)
     q, k, v = x[0], x[1], x[2]
@@ -105,16 +114,17 @@ def test_attention(lib, B, L, Cdim, heads):
 
 
 @pytest.mark.parametrize("B,H,W,p", [(3, 64, 64, 8), (2, 64, 64, 4), (1, 200, 200, 8), (2, 16, 16, 4), (2, 32, 48, 4)])
-def test_patchify(lib, B, H, W, p):
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_patchify(lib, B, H, W, p, fmt):
     x = torch.randn(B, 3, H, W, device="cuda")
     P = 3 * p * p
     Kp = (P + 63) // 64 * 64
     n = (H // p) * (W // p)
     L = n + 1
-    ap = torch.full((B * L, Kp), 9.0, device="cuda", dtype=torch.bfloat16)
-    _check(lib.ddc_k_patchify(x.data_ptr(), ap.data_ptr(), B, H, W, p, Kp, _stream()))
+    ap = torch.full((B * L, Kp), 9.0, device="cuda", dtype=torch.float16 if fmt else torch.bfloat16)
+    _check(lib.ddc_k_patchify(fmt, x.data_ptr(), ap.data_ptr(), B, H, W, p, Kp, _stream()))
     torch.cuda.synchronize()
-    ref = x.reshape(B, 3, H // p, p, W // p, p).permute(0, 2, 4, 1, 3, 5).reshape(B, n, P).to(torch.bfloat16)
+    ref = x.reshape(B, 3, H // p, p, W // p, p).permute(0, 2, 4, 1, 3, 5).reshape(B, n, P).to(ap.dtype)
     got = ap.reshape(B, L, Kp)
     assert torch.equal(got[:, 1:, :P], ref)
     assert torch.count_nonzero(got[:, 0]) == 0 and torch.count_nonzero(got[:, :, P:]) == 0
