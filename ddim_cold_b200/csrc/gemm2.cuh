@@ -5,7 +5,7 @@
 // A CTA (one per SM) walks 128-row M tiles round-robin.  Roles: warp 0 = TMA producer (the A
 // tile, K/64 boxes of 64x128, then the W tiles bn x 64 through a ring), warp 1 = tcgen05.mma
 // issuer (M=128, N=bn, K=16 per instruction, fp32 accumulators in TMEM), warp 2 = TMEM
-// allocator, warps 4-7 = epilogue (thread = one output row).  A is released K-block by
+// allocator, warps 4-11 = epilogue (thread = one output row, two warps per TMEM lane quarter).  A is released K-block by
 // K-block while the last N tile is being multiplied, so the next tile's A loads overlap it.
 //
 // Two flavours:
@@ -31,12 +31,13 @@ enum { S_BF16 = 0, S_BF16_GELU = 1, S_F32 = 2, R_RESID = 3, R_EMBED = 4 };
 
 constexpr int G2_BM = 128;
 constexpr int G2_BK = 64;
-constexpr int G2_THREADS = 256;
+constexpr int G2_THREADS = 384;             // warp0 TMA, warp1 MMA, warp2 TMEM, warp3 spare, warps4-11 epilogue
+constexpr int G2_EPI_WARPS = 8;             // two warps per TMEM lane quarter, alternating column chunks
 constexpr int G2_A_KB_BYTES = G2_BM * 128;
 constexpr int G2_SLOT_BYTES = 32 * 128;     // one epilogue warp's staging unit: 32 rows x 128 B
-constexpr int G2_ES_STREAM = 2;             // staging slots per epilogue warp
-constexpr int G2_ES_ROW = 4;
-constexpr int G2_PD_ROW = 2;                // residual chunks prefetched ahead per warp
+constexpr int G2_ES_STREAM = 1;             // staging slots per epilogue warp
+constexpr int G2_ES_ROW = 2;                // row-block: residual chunk in flight + chunk being processed
+constexpr int G2_TAIL_BYTES = 3072;         // barriers, TMEM slot, row-statistics exchange
 
 struct Gemm2Params {
     int M, N, K, bn, stages, num_tiles;
@@ -61,13 +62,22 @@ __host__ __device__ inline uint32_t g2_pow2_cols(uint32_t c) {
     return p;
 }
 
-inline size_t gemm2_smem_bytes(int K, int bn, int stages, bool rowblock) {
+// bias (and, row-block, LayerNorm gamma/beta) are staged in shared memory: with the full carve-out
+// given to shared memory there is no L1 left, and a per-chunk __ldg would pay an L2 round trip.
+__host__ __device__ inline size_t gemm2_param_bytes(int N, bool rowblock) { return static_cast<size_t>(rowblock ? 3 : 1) * N * 4; }
+
+inline size_t gemm2_smem_bytes(int K, int N, int bn, int stages, bool rowblock) {
     return 1024 + static_cast<size_t>(K / G2_BK) * G2_A_KB_BYTES + static_cast<size_t>(stages) * bn * 128 +
-           static_cast<size_t>(4) * (rowblock ? G2_ES_ROW : G2_ES_STREAM) * G2_SLOT_BYTES + 512;
+           static_cast<size_t>(G2_EPI_WARPS) * (rowblock ? G2_ES_ROW : G2_ES_STREAM) * G2_SLOT_BYTES +
+           ((gemm2_param_bytes(N, rowblock) + 127) & ~static_cast<size_t>(127)) + G2_TAIL_BYTES;
 }
 
 // byte offset of 16-byte chunk `j` of row `r` inside a 128-byte-swizzled 32-row slot
 __device__ __forceinline__ uint32_t slot_off(int r, int j) { return r * 128 + ((j ^ (r & 7)) << 4); }
+
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
 
 template <int EPI, bool F16, int CS>
 __global__ void __launch_bounds__(G2_THREADS, 1)
@@ -86,7 +96,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem_a + static_cast<size_t>(kblocks) * G2_A_KB_BYTES;
     uint8_t* smem_e = smem_b + static_cast<size_t>(p.stages) * b_stage_bytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_e + 4 * ES * G2_SLOT_BYTES);
+    float* smem_p = reinterpret_cast<float*>(smem_e + G2_EPI_WARPS * ES * G2_SLOT_BYTES);   // bias | gamma | beta
+    uint64_t* bars = reinterpret_cast<uint64_t*>(
+        reinterpret_cast<uint8_t*>(smem_p) + ((gemm2_param_bytes(p.N, ROWBLOCK) + 127) & ~static_cast<size_t>(127)));
     uint64_t* full_bar = bars;             // [8]  W ring: TMA -> MMA
     uint64_t* empty_bar = bars + 8;        // [8]  W ring: MMA -> TMA
     uint64_t* afull_bar = bars + 16;       // [8]  A K-block landed
@@ -95,6 +107,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     uint64_t* tempty_bar = bars + 36;      // [2]  accumulator drained
     uint64_t* res_bar = bars + 38;         // [16] residual chunk landed (per epilogue warp x slot)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 54);
+    float* red = reinterpret_cast<float*>(bars + 64);     // [2 stats][2 halves][128 rows] partial row statistics
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -120,14 +133,23 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             mbar_init(&aempty_bar[i], 1);
         }
         for (int i = 0; i < 4; ++i) mbar_init(&tfull_bar[i], 1);
-        mbar_init(&tempty_bar[0], 4);
-        mbar_init(&tempty_bar[1], 4);
+        mbar_init(&tempty_bar[0], G2_EPI_WARPS);
+        mbar_init(&tempty_bar[1], G2_EPI_WARPS);
         for (int i = 0; i < 16; ++i) mbar_init(&res_bar[i], 1);
         fence_barrier_init();
     }
     if (warp == 2) {
         tmem_alloc(tmem_slot, tmem_cols);
         tmem_relinquish();
+    }
+    if (warp >= 4) {
+        for (int i = threadIdx.x - 128; i < p.N; i += G2_EPI_WARPS * 32) {
+            if (EPI != R_EMBED) smem_p[i] = p.bias[i];
+            if (ROWBLOCK) {
+                smem_p[p.N + i] = p.ln_g[i];
+                smem_p[2 * p.N + i] = p.ln_b[i];
+            }
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -210,12 +232,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         }
     } else if (warp >= 4) {
         // ================================================================= epilogue
-        const int q = warp - 4;
-        uint8_t* my_slots = smem_e + static_cast<size_t>(q) * ES * G2_SLOT_BYTES;
+        // warp w drains TMEM lanes [32*(w%4), +32) (thread = one output row); the two warps of a lane
+        // quarter (hf = 0/1) take alternating column chunks.
+        const int q = warp & 3;
+        const int hf = (warp - 4) >> 2;
+        uint8_t* my_slots = smem_e + static_cast<size_t>(warp - 4) * ES * G2_SLOT_BYTES;
         const uint32_t lane_taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+        const float* s_bias = smem_p;
         uint32_t tcount = 0;
         if (!ROWBLOCK) {
-            uint32_t acc_it = 0, slot_it = 0;
+            uint32_t acc_it = 0;
+            const int cpn = p.bn / 64;              // 64-column chunks per N tile (bf16 flavours)
             for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
                 const int row0 = tile * G2_BM + q * 32;
                 const int row = row0 + lane;
@@ -225,7 +252,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     tc_fence_after();
                     const uint32_t t_row = lane_taddr + acc * acc_stride;
                     if (EPI == S_F32) {
-                        for (int c = 0; c < p.bn; c += 16) {
+                        for (int c = 16 * hf; c < p.bn; c += 32) {
                             float v[16];
                             tmem_ld16(t_row + c, v);
                             if (row < p.M) {
@@ -233,25 +260,26 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                                 float4* dst = reinterpret_cast<float4*>(p.out_f32 + static_cast<size_t>(row) * p.ld_f32 + n0);
 #pragma unroll
                                 for (int i = 0; i < 4; ++i) {
-                                    const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + 4 * i));
+                                    const float4 b = *reinterpret_cast<const float4*>(s_bias + n0 + 4 * i);
                                     dst[i] = make_float4(v[4 * i] + b.x, v[4 * i + 1] + b.y, v[4 * i + 2] + b.z,
                                                          v[4 * i + 3] + b.w);
                                 }
                             }
                         }
                     } else {
-                        for (int c = 0; c < p.bn; c += 64, ++slot_it) {
-                            uint8_t* slot = my_slots + (slot_it % ES) * G2_SLOT_BYTES;
-                            if (lane == 0) bulk_wait_read<ES - 1>();      // this slot's previous store has read it
+                        for (int c = 0; c < cpn; ++c) {
+                            if (((nt * cpn + c) & 1) != hf) continue;
+                            uint8_t* slot = my_slots;
+                            if (lane == 0) bulk_wait_read<0>();      // the slot's previous store has read it
                             __syncwarp();
-                            const int n0 = nt * p.bn + c;
+                            const int n0 = nt * p.bn + c * 64;
 #pragma unroll
                             for (int h = 0; h < 2; ++h) {
                                 float v[32];
-                                tmem_ld32(t_row + c + 32 * h, v);
+                                tmem_ld32(t_row + c * 64 + 32 * h, v);
 #pragma unroll
                                 for (int i = 0; i < 32; i += 4) {
-                                    const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + 32 * h + i));
+                                    const float4 b = *reinterpret_cast<const float4*>(s_bias + n0 + 32 * h + i);
                                     v[i] += b.x; v[i + 1] += b.y; v[i + 2] += b.z; v[i + 3] += b.w;
                                 }
                                 if (EPI == S_BF16_GELU) {
@@ -283,10 +311,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             }
         } else {
             // ---------------------------------------------------------- row-block flavour
-            const int nchunk = p.N / 32;            // fp32 chunks of 128 B per row
+            const int nchunk = p.N / 32;            // fp32 chunks of 128 B per row; this warp takes c % 2 == hf
             const float inv_n = 1.0f / static_cast<float>(p.N);
-            uint32_t ri = 0;                        // residual / staging slot counter (this warp)
-            uint32_t loads = 0;                     // residual loads issued so far (lane 0 bookkeeping = all lanes)
+            const float* s_gamma = smem_p + p.N;
+            const float* s_beta = smem_p + 2 * p.N;
+            float* red_sum = red + hf * 128 + q * 32 + lane;
+            float* red_sq = red + 256 + hf * 128 + q * 32 + lane;
+            const float* oth_sum = red + (hf ^ 1) * 128 + q * 32 + lane;
+            const float* oth_sq = red + 256 + (hf ^ 1) * 128 + q * 32 + lane;
+            uint64_t* my_res = res_bar + (warp - 4) * ES;
+            uint32_t ri = 0;                        // staging-slot counter (this warp)
+            uint32_t res_phase = 0;                 // per-slot parity of the residual barriers (bit s)
             for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
                 const int row0 = tile * G2_BM + q * 32;
                 const int row = row0 + lane;
@@ -300,50 +335,48 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     embed_pos = p.posb + static_cast<size_t>(l) * p.N;
                     embed_time = p.time_tab + static_cast<size_t>(t) * p.N;
                 }
-                if (EPI == R_RESID) {
-                    // slots may still be the source of the previous tile's XN stores
+                if (EPI == R_RESID && hf < nchunk) {
                     if (lane == 0) {
-                        bulk_wait_read<0>();
-                        for (int c = 0; c < G2_PD_ROW && c < nchunk; ++c) {
-                            const uint32_t s = (ri + c) % ES;
-                            mbar_arrive_expect_tx(&res_bar[q * ES + s], G2_SLOT_BYTES);
-                            tma_load_2d(my_slots + s * G2_SLOT_BYTES, &tmR, &res_bar[q * ES + s], c * 32, row0);
-                        }
+                        bulk_wait_read<0>();        // slots may still feed the previous tile's XN stores
+                        const uint32_t s = ri % ES;
+                        mbar_arrive_expect_tx(&my_res[s], G2_SLOT_BYTES);
+                        tma_load_2d(my_slots + s * G2_SLOT_BYTES, &tmR, &my_res[s], hf * 32, row0);
                     }
                     __syncwarp();
                 }
                 float sum = 0.f;
-                for (int c = 0; c < nchunk; ++c, ++ri) {
+                int waited_nt = -1;
+                for (int c = hf; c < nchunk; c += 2, ++ri) {
                     const uint32_t s = ri % ES;
                     uint8_t* slot = my_slots + s * G2_SLOT_BYTES;
                     if (lane == 0) {
-                        bulk_wait_read<1>();        // every store but the most recent has released its slot
-                        if (EPI == R_RESID && c + G2_PD_ROW < nchunk) {
-                            const uint32_t s2 = (ri + G2_PD_ROW) % ES;
-                            mbar_arrive_expect_tx(&res_bar[q * ES + s2], G2_SLOT_BYTES);
-                            tma_load_2d(my_slots + s2 * G2_SLOT_BYTES, &tmR, &res_bar[q * ES + s2],
-                                        (c + G2_PD_ROW) * 32, row0);
+                        bulk_wait_read<0>();        // the other slot's store (previous chunk) has released it
+                        if (EPI == R_RESID && c + 2 < nchunk) {
+                            const uint32_t s2 = (ri + 1) % ES;
+                            mbar_arrive_expect_tx(&my_res[s2], G2_SLOT_BYTES);
+                            tma_load_2d(my_slots + s2 * G2_SLOT_BYTES, &tmR, &my_res[s2], (c + 2) * 32, row0);
                         }
                     }
                     __syncwarp();
                     const int n0 = c * 32;
-                    if (n0 % p.bn == 0) {
-                        mbar_wait(&tfull_bar[n0 / p.bn], tcount & 1);
+                    const int nt = n0 / p.bn;
+                    if (nt != waited_nt) {
+                        mbar_wait(&tfull_bar[nt], tcount & 1);
                         tc_fence_after();
+                        waited_nt = nt;
                     }
                     float v[32];
                     tmem_ld32(lane_taddr + n0, v);
                     if (EPI == R_RESID) {
-                        // per-slot phase: this warp has waited on slot s exactly (loads_done_on_s) times
-                        mbar_wait(&res_bar[q * ES + s], (loads / ES) & 1);
+                        mbar_wait(&my_res[s], (res_phase >> s) & 1);
+                        res_phase ^= (1u << s);
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             const float4 r = *reinterpret_cast<const float4*>(slot + slot_off(lane, j));
-                            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + 4 * j));
+                            const float4 b = *reinterpret_cast<const float4*>(s_bias + n0 + 4 * j);
                             v[4 * j] += r.x + b.x; v[4 * j + 1] += r.y + b.y;
                             v[4 * j + 2] += r.z + b.z; v[4 * j + 3] += r.w + b.w;
                         }
-                        ++loads;
                     } else {
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
@@ -367,10 +400,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                         bulk_commit();
                     }
                 }
-                // ---- exact two-pass variance, then LayerNorm -> bf16 XN
-                const float mean = sum * inv_n;
+                // ---- row statistics: exact two-pass variance; the two column halves exchange partials
+                *red_sum = sum;
+                tc_fence_before();                  // the partner's pass 3 reads TMEM columns this warp stored
+                named_bar_sync(1 + q, 64);
+                tc_fence_after();
+                const float mean = (sum + *oth_sum) * inv_n;
                 float sq = 0.f;
-                for (int c = 0; c < nchunk; ++c) {
+                for (int c = hf; c < nchunk; c += 2) {
                     float v[32];
                     tmem_ld32(lane_taddr + c * 32, v);
 #pragma unroll
@@ -379,10 +416,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                         sq += d * d;
                     }
                 }
-                const float rstd = rsqrtf(sq * inv_n + p.ln_eps);
-                for (int c = 0; c < p.N / 64; ++c, ++ri) {
+                *red_sq = sq;
+                named_bar_sync(1 + q, 64);
+                const float rstd = rsqrtf((sq + *oth_sq) * inv_n + p.ln_eps);
+                for (int c = hf; c < p.N / 64; c += 2, ++ri) {
                     uint8_t* slot = my_slots + (ri % ES) * G2_SLOT_BYTES;
-                    if (lane == 0) bulk_wait_read<1>();
+                    if (lane == 0) bulk_wait_read<ES - 1>();
                     __syncwarp();
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
@@ -391,10 +430,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                         tmem_ld32(lane_taddr + n0, v);
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            const float4 g0 = __ldg(reinterpret_cast<const float4*>(p.ln_g + n0 + 8 * j));
-                            const float4 g1 = __ldg(reinterpret_cast<const float4*>(p.ln_g + n0 + 8 * j + 4));
-                            const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.ln_b + n0 + 8 * j));
-                            const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.ln_b + n0 + 8 * j + 4));
+                            const float4 g0 = *reinterpret_cast<const float4*>(s_gamma + n0 + 8 * j);
+                            const float4 g1 = *reinterpret_cast<const float4*>(s_gamma + n0 + 8 * j + 4);
+                            const float4 b0 = *reinterpret_cast<const float4*>(s_beta + n0 + 8 * j);
+                            const float4 b1 = *reinterpret_cast<const float4*>(s_beta + n0 + 8 * j + 4);
                             uint4 o;
                             o.x = pack2<F16>((v[8 * j] - mean) * rstd * g0.x + b0.x, (v[8 * j + 1] - mean) * rstd * g0.y + b0.y);
                             o.y = pack2<F16>((v[8 * j + 2] - mean) * rstd * g0.z + b0.z, (v[8 * j + 3] - mean) * rstd * g0.w + b0.w);
