@@ -159,6 +159,33 @@ __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t adesc, ui
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// One K block (64 elements = four K=16 instructions) of D[tmem] (+)= A * B.  The descriptors address the
+// first 32-byte K slice; consecutive slices are +32 B = +2 in the descriptor's 16-byte address units.
+// A single asm statement with warp-uniform operands lets ptxas keep everything in uniform registers
+// and issue the four UTCHMMA back to back (no per-instruction elect/broadcast sequence).
+__device__ __forceinline__ void umma_kblock(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate_first) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 a1, b1;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "setp.eq.b32 q, 0, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "add.u64 a1, %1, 2;\n\tadd.u64 b1, %2, 2;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, q;\n\t"
+        "add.u64 a1, %1, 4;\n\tadd.u64 b1, %2, 4;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, q;\n\t"
+        "add.u64 a1, %1, 6;\n\tadd.u64 b1, %2, 6;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, q;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate_first)
+        : "memory");
+}
+// True in exactly one lane of the (fully active) warp; ptxas recognises the pattern and needs no
+// per-instruction leader election for the single-thread tcgen05 / TMA instructions that follow.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 // Arrive on an mbarrier once every tcgen05 op this thread issued so far has completed.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))

@@ -190,8 +190,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     } else if (warp == 1) {
         // ================================================================= MMA issuer
         const uint32_t idesc = umma_idesc_16bit(G2_BM, static_cast<uint32_t>(p.bn), F16);
-        const uint32_t a_base = smem_u32(smem_a);
-        const uint32_t b_base = smem_u32(smem_b);
+        const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);     // warp-uniform for ptxas
+        const uint64_t ad0 = umma_desc_sw128(smem_u32(smem_a));
+        const uint64_t bd0 = umma_desc_sw128(smem_u32(smem_b));
+        const uint32_t b_stage_units = b_stage_bytes >> 4;
         uint32_t stage = 0, phase = 0, tcount = 0, acc_it = 0;
         for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
             for (int nt = 0; nt < num_nt; ++nt) {
@@ -199,12 +201,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 uint64_t* done_bar;
                 if (ROWBLOCK) {
                     if (nt == 0) mbar_wait(&tempty_bar[0], (tcount & 1) ^ 1);
-                    d_tmem = tmem_base + static_cast<uint32_t>(nt * p.bn);
+                    d_tmem = tb + static_cast<uint32_t>(nt * p.bn);
                     done_bar = &tfull_bar[nt];
                 } else {
                     const uint32_t acc = acc_it & 1;
                     mbar_wait(&tempty_bar[acc], ((acc_it >> 1) & 1) ^ 1);
-                    d_tmem = tmem_base + acc * acc_stride;
+                    d_tmem = tb + acc * acc_stride;
                     done_bar = &tfull_bar[acc];
                     ++acc_it;
                 }
@@ -213,13 +215,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     if (nt == 0) mbar_wait(&afull_bar[kb], tcount & 1);
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    if (lane == 0) {
-#pragma unroll
-                        for (int k = 0; k < G2_BK / 16; ++k) {
-                            const uint64_t ad = umma_desc_sw128(a_base + kb * G2_A_KB_BYTES + k * 32);
-                            const uint64_t bd = umma_desc_sw128(b_base + stage * b_stage_bytes + k * 32);
-                            umma_bf16_ss(d_tmem, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
-                        }
+                    if (elect_one()) {
+                        umma_kblock(d_tmem, ad0 + static_cast<uint64_t>(kb * (G2_A_KB_BYTES >> 4)),
+                                    bd0 + static_cast<uint64_t>(stage * b_stage_units), idesc, kb != 0 ? 1u : 0u);
                         if (CS == 1) umma_commit(&empty_bar[stage]);
                         else umma_commit_mcast(&empty_bar[stage], kMask);
                         if (nt == num_nt - 1) umma_commit(&aempty_bar[kb]);
