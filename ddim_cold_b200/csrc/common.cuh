@@ -89,16 +89,18 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
         : "memory");
 }
 
-// Same, delivered to the same smem offset (and signalling the same barrier offset) in every CTA of
-// `cta_mask` within the cluster: one L2 read feeds all of them.
-__device__ __forceinline__ void tma_load_2d_mcast(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
-                                                  uint16_t cta_mask) {
+// CTA-pair load: the data lands in THIS CTA's shared memory, the transaction bytes are credited to the
+// barrier at the same offset in the pair's leader CTA (even rank), which is the one that issues the MMAs.
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;      // clears the CTA-rank bit of a shared::cluster address
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
     asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-        " [%0], [%1, {%3, %4}], [%2], %5;"
-        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1),
-          "h"(cta_mask)
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
         : "memory");
+}
+// Arrive on the barrier at this offset in the pair's leader CTA (works from either CTA of the pair).
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerBitMask) : "memory");
 }
 
 // 2-D tiled store smem -> global (bulk async group); rows / columns outside the tensor map are clipped
@@ -115,16 +117,26 @@ __device__ __forceinline__ void bulk_wait_read() {   // at most N committed grou
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // ----------------------------------------------------------------------------- TMEM
+// CG = 1: this CTA's tensor memory.  CG = 2: the same columns in both CTAs of a pair (issued by the
+// same warp id in each CTA, writing the same shared-memory slot offset).
+template <int CG = 1>
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_slot, uint32_t ncols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)),
-                 "r"(ncols)
-                 : "memory");
+    if (CG == 2)
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)),
+                     "r"(ncols) : "memory");
+    else
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)),
+                     "r"(ncols) : "memory");
 }
+template <int CG = 1>
 __device__ __forceinline__ void tmem_relinquish() {
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (CG == 2) asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    else asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
 }
+template <int CG = 1>
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+    if (CG == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
 
 // Shared-memory matrix descriptor for a K-major bf16 operand tile stored as rows of 128 B
@@ -163,21 +175,27 @@ __device__ __forceinline__ void umma_bf16_ss(uint32_t tmem_d, uint64_t adesc, ui
 // first 32-byte K slice; consecutive slices are +32 B = +2 in the descriptor's 16-byte address units.
 // A single asm statement with warp-uniform operands lets ptxas keep everything in uniform registers
 // and issue the four UTCHMMA back to back (no per-instruction elect/broadcast sequence).
+// CG = 2: one instruction drives both SMs of a CTA pair (M = 256): each CTA supplies its own 128 rows of
+// A and half of the N rows of B from the same shared-memory offsets, and receives its 128 rows of D.
+#define DDC_UMMA_KBLOCK_ASM(CGS)                                                           \
+    asm volatile(                                                                          \
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 a1, b1;\n\t"                                   \
+        "setp.ne.b32 p, %4, 0;\n\t"                                                        \
+        "setp.eq.b32 q, 0, 0;\n\t"                                                         \
+        "tcgen05.mma.cta_group::" CGS ".kind::f16 [%0], %1, %2, %3, p;\n\t"                \
+        "add.u64 a1, %1, 2;\n\tadd.u64 b1, %2, 2;\n\t"                                     \
+        "tcgen05.mma.cta_group::" CGS ".kind::f16 [%0], a1, b1, %3, q;\n\t"                \
+        "add.u64 a1, %1, 4;\n\tadd.u64 b1, %2, 4;\n\t"                                     \
+        "tcgen05.mma.cta_group::" CGS ".kind::f16 [%0], a1, b1, %3, q;\n\t"                \
+        "add.u64 a1, %1, 6;\n\tadd.u64 b1, %2, 6;\n\t"                                     \
+        "tcgen05.mma.cta_group::" CGS ".kind::f16 [%0], a1, b1, %3, q;\n\t}"               \
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate_first)           \
+        : "memory")
+template <int CG = 1>
 __device__ __forceinline__ void umma_kblock(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                             uint32_t accumulate_first) {
-    asm volatile(
-        "{\n\t.reg .pred p, q;\n\t.reg .b64 a1, b1;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "setp.eq.b32 q, 0, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-        "add.u64 a1, %1, 2;\n\tadd.u64 b1, %2, 2;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, q;\n\t"
-        "add.u64 a1, %1, 4;\n\tadd.u64 b1, %2, 4;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, q;\n\t"
-        "add.u64 a1, %1, 6;\n\tadd.u64 b1, %2, 6;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, q;\n\t}"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate_first)
-        : "memory");
+    if (CG == 2) DDC_UMMA_KBLOCK_ASM("2");
+    else DDC_UMMA_KBLOCK_ASM("1");
 }
 // True in exactly one lane of the (fully active) warp; ptxas recognises the pattern and needs no
 // per-instruction leader election for the single-thread tcgen05 / TMA instructions that follow.
@@ -192,11 +210,12 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                  : "memory");
 }
 
-// Same, arriving on the barrier at this offset in every CTA of `cta_mask`.
-__device__ __forceinline__ void umma_commit_mcast(uint64_t* bar, uint16_t cta_mask) {
+// CTA-pair commit: arrives on the barrier at this offset in BOTH CTAs once every pair-wide tcgen05 op
+// issued so far by this thread has completed.
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
     asm volatile(
-        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-        ::"r"(smem_u32(bar)), "h"(cta_mask)
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+        ::"r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3))
         : "memory");
 }
 __device__ __forceinline__ uint32_t cluster_ctarank() {

@@ -89,14 +89,14 @@ static int make_tmap(CUtensorMap* m, bool f32, const void* base, uint64_t rows, 
 }
 
 // ------------------------------------------------------------------------------- GEMM launch
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
 static int pick_from(int N, const int* cands, int n) {
     for (int i = 0; i < n; ++i)
         if (N % cands[i] == 0) return cands[i];
     return 0;
-}
-static int env_int(const char* name, int dflt) {
-    const char* v = getenv(name);
-    return (v && *v) ? atoi(v) : dflt;
 }
 static int pick_bn_stream(int N) {
     const int forced = env_int("DDC_BN_STREAM", 0);      // tuning aid
@@ -110,7 +110,7 @@ static int pick_bn_row(int N) { const int c[] = {128, 64}; return pick_from(N, c
 static int pick_stages2(int K, int N, int bn, bool rowblock) {
     const long budget = 227 * 1024 - static_cast<long>(gemm2_smem_bytes(K, N, bn, 0, rowblock));
     long s = budget / (static_cast<long>(bn) * 128);
-    if (s > 6) s = 6;
+    if (s > 8) s = 8;
     const int cap = env_int("DDC_MAX_STAGES", 0);          // tuning aid
     if (cap >= 2 && s > cap) s = cap;
     return static_cast<int>(s);
@@ -159,7 +159,11 @@ static int launch_gemm2_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, con
 }
 
 // W tiles are multicast to the `cs` CTAs of a cluster; tmB's box must hold bn/cs rows.
-static int gemm_cluster_size(int M) { return (M + G2_BM - 1) / G2_BM >= 2 ? 2 : 1; }
+static int gemm_cluster_size(int M) {
+    const int forced = env_int("DDC_CLUSTER", 0);        // tuning aid
+    if (forced == 1 || forced == 2) return forced;
+    return (M + G2_BM - 1) / G2_BM >= 2 ? 2 : 1;
+}
 
 template <int EPI>
 static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR,
@@ -171,7 +175,7 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
         (p.bn / cs) % 8 != 0)
         return fail(DDC_E_INVALID, "gemm: unsupported M=%d N=%d K=%d bn=%d stages=%d epi=%d cs=%d", p.M, p.N, p.K, p.bn,
                     p.stages, EPI, cs);
-    const size_t smem = gemm2_smem_bytes(p.K, p.N, p.bn, p.stages, rowblock);
+    const size_t smem = gemm2_smem_bytes(p.K, p.N, p.bn / cs, p.stages, rowblock);
     if (smem > 227 * 1024) return fail(DDC_E_INVALID, "gemm: %zu B of shared memory needed", smem);
     p.num_tiles = ((p.M + G2_BM - 1) / G2_BM + cs - 1) / cs * cs;
     if (f16) {
@@ -559,7 +563,7 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     MARK(KC_PATCHIFY);
     const LayerW& l0 = pl->layers[0];
     Gemm2Params g{};
-    g.M = M; g.N = C; g.K = pl->Kp; g.bn = pl->bn_row; g.stages = pick_stages2(g.K, g.N, g.bn, true);
+    g.M = M; g.N = C; g.K = pl->Kp; g.bn = pl->bn_row; g.stages = pick_stages2(g.K, g.N, g.bn / cs, true);
     g.ln_g = l0.ln1_g; g.ln_b = l0.ln1_b; g.ln_eps = 1e-5f;
     g.posb = pl->posb; g.L = L; g.time_tab = pl->time_tab; g.t_img = t_img; g.tbl = pl->tbl; g.cur = pl->ctr; g.B = B;
     TRY((launch_gemm2<R_EMBED>(pl->tm_Ap, pl->tm_wpatch[cs - 1], pl->st_X, pl->tm_Xld, pl->st_XN, g, f16, cs, st)));
@@ -567,19 +571,19 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     for (int i = 0; i < s.depth; ++i) {
         LayerW& l = pl->layers[i];
         Gemm2Params q{};
-        q.M = M; q.N = 3 * C; q.K = C; q.bn = pl->bn_qkv; q.stages = pick_stages2(q.K, q.N, q.bn, false);
+        q.M = M; q.N = 3 * C; q.K = C; q.bn = pl->bn_qkv; q.stages = pick_stages2(q.K, q.N, q.bn / cs, false);
         q.bias = l.b_qkv;
         TRY((launch_gemm2<S_BF16>(pl->tm_XN, l.tm_qkv[cs - 1], pl->st_QKV, pl->tm_Xld, pl->st_XN, q, f16, cs, st)));
         MARK(KC_QKV);
         TRY(run_attention(pl->QKV, pl->O, B, L, C, s.heads, f16, st));
         MARK(KC_ATTN);
         Gemm2Params r{};
-        r.M = M; r.N = C; r.K = C; r.bn = pl->bn_row; r.stages = pick_stages2(r.K, r.N, r.bn, true);
+        r.M = M; r.N = C; r.K = C; r.bn = pl->bn_row; r.stages = pick_stages2(r.K, r.N, r.bn / cs, true);
         r.bias = l.b_proj; r.ln_g = l.ln2_g; r.ln_b = l.ln2_b; r.ln_eps = 1e-5f;
         TRY((launch_gemm2<R_RESID>(pl->tm_O, l.tm_proj[cs - 1], pl->st_X, pl->tm_Xld, pl->st_XN, r, f16, cs, st)));
         MARK(KC_PROJ);
         Gemm2Params f{};
-        f.M = M; f.N = C; f.K = C; f.bn = pl->bn_fc1; f.stages = pick_stages2(f.K, f.N, f.bn, false);
+        f.M = M; f.N = C; f.K = C; f.bn = pl->bn_fc1; f.stages = pick_stages2(f.K, f.N, f.bn / cs, false);
         f.bias = l.b_fc1;
         TRY((launch_gemm2<S_BF16_GELU>(pl->tm_XN, l.tm_fc1[cs - 1], pl->st_Hd, pl->tm_Xld, pl->st_XN, f, f16, cs, st)));
         MARK(KC_FC1);
@@ -590,7 +594,7 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
         MARK(KC_FC2);
     }
     Gemm2Params h{};
-    h.M = M; h.N = pl->P; h.K = C; h.bn = pl->bn_head; h.stages = pick_stages2(h.K, h.N, h.bn, false);
+    h.M = M; h.N = pl->P; h.K = C; h.bn = pl->bn_head; h.stages = pick_stages2(h.K, h.N, h.bn / cs, false);
     h.bias = pl->b_head; h.out_f32 = pl->Y; h.ld_f32 = pl->P;
     TRY((launch_gemm2<S_F32>(pl->tm_XN, pl->tm_whead[cs - 1], pl->st_XN, pl->tm_Xld, pl->st_XN, h, f16, cs, st)));
     MARK(KC_HEAD);
@@ -778,7 +782,7 @@ extern "C" int ddc_k_gemm(int32_t fmt, int32_t epi, int32_t M, int32_t N, int32_
     TRY(make_tmap(&tmA, false, A, Mp, K, G2_BM));
     TRY(make_tmap(&tmB, false, W, N, K, bn / cs));
     Gemm2Params p{};
-    p.M = M; p.N = N; p.K = K; p.bn = bn; p.stages = pick_stages2(K, N, bn, false); p.bias = bias;
+    p.M = M; p.N = N; p.K = K; p.bn = bn; p.stages = pick_stages2(K, N, bn / cs, false); p.bias = bias;
     switch (epi) {
         case S_BF16:
             TRY(make_tmap(&tmO, false, out, M, N, 32));
@@ -810,7 +814,7 @@ extern "C" int ddc_k_gemm_resid_ln(int32_t fmt, int32_t M, int32_t C, int32_t K,
     TRY(make_tmap(&tmR, true, x, Mp, C, 32));
     TRY(make_tmap(&tmN, false, xn, M, C, 32));
     Gemm2Params p{};
-    p.M = M; p.N = C; p.K = K; p.bn = bn; p.stages = pick_stages2(K, C, bn, true); p.bias = bias;
+    p.M = M; p.N = C; p.K = K; p.bn = bn; p.stages = pick_stages2(K, C, bn / cs, true); p.bias = bias;
     p.ln_g = ln_g; p.ln_b = ln_b; p.ln_eps = 1e-5f;
     return launch_gemm2<R_RESID>(tmA, tmB, tmO, tmR, tmN, p, fmt == 1, cs, st);
 }

@@ -2,6 +2,10 @@
 //
 //   OUT[M, N] = epilogue( A[M, K] * W[N, K]^T ),  A and W bf16 K-major, K <= 512.
 //
+// With CS = 2 two CTAs (one per SM of a TPC) form a pair: each stages its own 128-row A tile and HALF of
+// every W tile, and the pair's leader issues cta_group::2 MMAs (M = 256) that read both halves, so every
+// SM ingests only half of the weight stream -- the L2->SM fabric (~6 TB/s chip-wide), not the tensor
+// pipe, is what bounds these GEMMs.
 // A CTA (one per SM) walks 128-row M tiles round-robin.  Roles: warp 0 = TMA producer (the A
 // tile, K/64 boxes of 64x128, then the W tiles bn x 64 through a ring), warp 1 = tcgen05.mma
 // issuer (M=128, N=bn, K=16 per instruction, fp32 accumulators in TMEM), warp 2 = TMEM
@@ -92,7 +96,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
     const int kblocks = p.K / G2_BK;
     const int num_nt = p.N / p.bn;
-    const uint32_t b_stage_bytes = static_cast<uint32_t>(p.bn) * 128u;
+    const uint32_t b_stage_bytes = static_cast<uint32_t>(p.bn / CS) * 128u;   // this CTA's share of a W tile
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem_a + static_cast<size_t>(kblocks) * G2_A_KB_BYTES;
     uint8_t* smem_e = smem_b + static_cast<size_t>(p.stages) * b_stage_bytes;
@@ -111,12 +115,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    // CTAs of a cluster take adjacent M tiles and share every W tile through TMA multicast; p.num_tiles is a
-    // multiple of CS, so all CTAs of a cluster run the same number of iterations (surplus tiles store nothing).
+    // The CTAs of a pair take adjacent M tiles; p.num_tiles is a multiple of CS, so both run the same number of
+    // iterations (a surplus tile stores nothing).
     const uint32_t crank = CS > 1 ? cluster_ctarank() : 0u;
     const int first_tile = static_cast<int>((blockIdx.x / CS) * CS + crank);
     const int tile_step = gridDim.x;
-    constexpr uint16_t kMask = static_cast<uint16_t>((1u << CS) - 1u);
+    const bool leader = crank == 0;
     const uint32_t acc_stride = g2_pow2_cols(p.bn);
     const uint32_t tmem_cols = ROWBLOCK ? g2_pow2_cols(p.N) : g2_pow2_cols(2 * acc_stride);
 
@@ -128,19 +132,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (ROWBLOCK) tma_prefetch_desc(&tmN);
         for (int i = 0; i < 8; ++i) {
             mbar_init(&full_bar[i], 1);
-            mbar_init(&empty_bar[i], CS);        // every CTA of the cluster must have consumed the stage
+            mbar_init(&empty_bar[i], 1);
             mbar_init(&afull_bar[i], 1);
             mbar_init(&aempty_bar[i], 1);
         }
         for (int i = 0; i < 4; ++i) mbar_init(&tfull_bar[i], 1);
-        mbar_init(&tempty_bar[0], G2_EPI_WARPS);
-        mbar_init(&tempty_bar[1], G2_EPI_WARPS);
+        mbar_init(&tempty_bar[0], G2_EPI_WARPS * CS);     // the leader hears from both CTAs' epilogue warps
+        mbar_init(&tempty_bar[1], G2_EPI_WARPS * CS);
         for (int i = 0; i < 16; ++i) mbar_init(&res_bar[i], 1);
         fence_barrier_init();
     }
     if (warp == 2) {
-        tmem_alloc(tmem_slot, tmem_cols);
-        tmem_relinquish();
+        tmem_alloc<CS>(tmem_slot, tmem_cols);
+        tmem_relinquish<CS>();
     }
     if (warp >= 4) {
         for (int i = threadIdx.x - 128; i < p.N; i += G2_EPI_WARPS * 32) {
@@ -165,21 +169,25 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 const int m0 = tile * G2_BM;
                 for (int kb = 0; kb < kblocks; ++kb) {
                     mbar_wait(&aempty_bar[kb], (tcount & 1) ^ 1);
-                    mbar_arrive_expect_tx(&afull_bar[kb], G2_A_KB_BYTES);
-                    tma_load_2d(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0);
+                    if (CS == 1) {
+                        mbar_arrive_expect_tx(&afull_bar[kb], G2_A_KB_BYTES);
+                        tma_load_2d(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0);
+                    } else {      // both CTAs' bytes are credited to the leader's barrier
+                        if (leader) mbar_arrive_expect_tx(&afull_bar[kb], CS * G2_A_KB_BYTES);
+                        tma_load_2d_pair(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0);
+                    }
                 }
                 for (int nt = 0; nt < num_nt; ++nt) {
                     for (int kb = 0; kb < kblocks; ++kb) {
                         mbar_wait(&empty_bar[stage], phase ^ 1);
-                        mbar_arrive_expect_tx(&full_bar[stage], b_stage_bytes);
                         if (CS == 1) {
+                            mbar_arrive_expect_tx(&full_bar[stage], b_stage_bytes);
                             tma_load_2d(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
                                         kb * G2_BK, nt * p.bn);
-                        } else {      // this CTA fetches rows [crank*bn/CS, +bn/CS) of the W tile for the whole cluster
-                            const uint32_t slice = b_stage_bytes / CS;
-                            tma_load_2d_mcast(smem_b + static_cast<size_t>(stage) * b_stage_bytes + crank * slice, &tmB,
-                                              &full_bar[stage], kb * G2_BK, nt * p.bn + static_cast<int>(crank) * (p.bn / CS),
-                                              kMask);
+                        } else {      // this CTA stages rows [crank*bn/2, +bn/2) of the W tile
+                            if (leader) mbar_arrive_expect_tx(&full_bar[stage], CS * b_stage_bytes);
+                            tma_load_2d_pair(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
+                                             kb * G2_BK, nt * p.bn + static_cast<int>(crank) * (p.bn / CS));
                         }
                         if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
                     }
@@ -187,9 +195,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             }
         }
         __syncwarp();
-    } else if (warp == 1) {
-        // ================================================================= MMA issuer
-        const uint32_t idesc = umma_idesc_16bit(G2_BM, static_cast<uint32_t>(p.bn), F16);
+    } else if (warp == 1 && leader) {
+        // ================================================================= MMA issuer (pair leader only)
+        const uint32_t idesc = umma_idesc_16bit(G2_BM * CS, static_cast<uint32_t>(p.bn), F16);
         const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);     // warp-uniform for ptxas
         const uint64_t ad0 = umma_desc_sw128(smem_u32(smem_a));
         const uint64_t bd0 = umma_desc_sw128(smem_u32(smem_b));
@@ -216,12 +224,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     if (elect_one()) {
-                        umma_kblock(d_tmem, ad0 + static_cast<uint64_t>(kb * (G2_A_KB_BYTES >> 4)),
-                                    bd0 + static_cast<uint64_t>(stage * b_stage_units), idesc, kb != 0 ? 1u : 0u);
-                        if (CS == 1) umma_commit(&empty_bar[stage]);
-                        else umma_commit_mcast(&empty_bar[stage], kMask);
-                        if (nt == num_nt - 1) umma_commit(&aempty_bar[kb]);
-                        if (kb == kblocks - 1) umma_commit(done_bar);
+                        umma_kblock<CS>(d_tmem, ad0 + static_cast<uint64_t>(kb * (G2_A_KB_BYTES >> 4)),
+                                        bd0 + static_cast<uint64_t>(stage * b_stage_units), idesc, kb != 0 ? 1u : 0u);
+                        if (CS == 1) {
+                            umma_commit(&empty_bar[stage]);
+                            if (nt == num_nt - 1) umma_commit(&aempty_bar[kb]);
+                            if (kb == kblocks - 1) umma_commit(done_bar);
+                        } else {      // both CTAs' producers / epilogues are released
+                            umma_commit_pair(&empty_bar[stage]);
+                            if (nt == num_nt - 1) umma_commit_pair(&aempty_bar[kb]);
+                            if (kb == kblocks - 1) umma_commit_pair(done_bar);
+                        }
                     }
                     __syncwarp();
                     if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
@@ -304,7 +317,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     }
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+                    if (lane == 0) { if (CS == 1) mbar_arrive(&tempty_bar[acc]); else mbar_arrive_leader(&tempty_bar[acc]); }
                 }
             }
         } else {
@@ -449,7 +462,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 }
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&tempty_bar[0]);
+                if (lane == 0) { if (CS == 1) mbar_arrive(&tempty_bar[0]); else mbar_arrive_leader(&tempty_bar[0]); }
             }
         }
         if (lane == 0) bulk_wait_all();      // smem must outlive the last TMA stores
@@ -459,7 +472,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     tc_fence_before();
     __syncthreads();
     if (CS > 1) cluster_sync_all();              // no CTA leaves while a peer may still write its smem / barriers
-    if (warp == 2) tmem_dealloc(tmem_base, tmem_cols);
+    if (warp == 2) tmem_dealloc<CS>(tmem_base, tmem_cols);
 }
 
 }  // namespace ddc
