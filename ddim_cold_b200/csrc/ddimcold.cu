@@ -88,33 +88,6 @@ static int make_tmap(CUtensorMap* m, bool f32, const void* base, uint64_t rows, 
     return DDC_OK;
 }
 
-// GEMM operand [rows, K] (K-major 16-bit) viewed as {64, rows, K/64}: one box = `gk` K blocks of `box_rows` rows,
-// each landing in shared memory as a 128-byte-swizzled [box_rows x 128 B] tile.
-static int make_tmap_operand(CUtensorMap* m, const void* base, uint64_t rows, uint64_t K, uint32_t box_rows, uint32_t gk) {
-    EncodeTiledFn enc;
-    TRY(get_encode_fn(&enc));
-    if (K % 64 != 0 || rows == 0 || box_rows == 0 || box_rows > 256 || gk == 0 || (K / 64) % gk != 0 ||
-        (reinterpret_cast<uintptr_t>(base) & 0xF) != 0)
-        return fail(DDC_E_INVALID, "operand map: rows=%llu K=%llu box_rows=%u gk=%u base=%p", (unsigned long long)rows,
-                    (unsigned long long)K, box_rows, gk, base);
-    cuuint64_t dims[3] = {64, rows, K / 64};
-    cuuint64_t strides[2] = {K * 2, 128};
-    cuuint32_t box[3] = {64, box_rows, gk};
-    cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(DDC_E_CUDA, "cuTensorMapEncodeTiled(3d) -> %d", static_cast<int>(r));
-    return DDC_OK;
-}
-
-static int pick_gk(int K) {
-    const int kb = K / 64;
-    if (kb % 3 == 0) return 3;
-    if (kb % 2 == 0) return 2;
-    return 1;
-}
-
 // ------------------------------------------------------------------------------- GEMM launch
 static int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
@@ -128,17 +101,15 @@ static int pick_from(int N, const int* cands, int n) {
 static int pick_bn_stream(int N) {
     const int forced = env_int("DDC_BN_STREAM", 0);      // tuning aid
     if (forced > 0 && N % forced == 0 && forced % 64 == 0) return forced;
-    const int c[] = {128, 192, 256, 64};      // 128: two 64-column chunks per N tile (one per epilogue warp of a
-    return pick_from(N, c, 4);                // lane quarter) and four accumulator stages in TMEM
+    const int c[] = {256, 192, 128, 64};
+    return pick_from(N, c, 4);
 }
 static int pick_bn_f32(int N) { const int c[] = {256, 192, 128, 96, 64, 48, 32, 16}; return pick_from(N, c, 8); }
 static int pick_bn_row(int N) { const int c[] = {128, 64}; return pick_from(N, c, 2); }
 
-// `bn_cta` = rows of a W tile staged by one CTA (bn / cluster size)
-static int pick_stages2(int K, int N, int bn_cta, bool rowblock) {
-    const long stage = static_cast<long>(pick_gk(K)) * bn_cta * 128;
-    const long budget = 227 * 1024 - static_cast<long>(gemm2_smem_bytes(K, N, 0, 0, rowblock));
-    long s = budget / stage;
+static int pick_stages2(int K, int N, int bn, bool rowblock) {
+    const long budget = 227 * 1024 - static_cast<long>(gemm2_smem_bytes(K, N, bn, 0, rowblock));
+    long s = budget / (static_cast<long>(bn) * 128);
     if (s > 8) s = 8;
     const int cap = env_int("DDC_MAX_STAGES", 0);          // tuning aid
     if (cap >= 2 && s > cap) s = cap;
@@ -204,8 +175,7 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
         (p.bn / cs) % 8 != 0)
         return fail(DDC_E_INVALID, "gemm: unsupported M=%d N=%d K=%d bn=%d stages=%d epi=%d cs=%d", p.M, p.N, p.K, p.bn,
                     p.stages, EPI, cs);
-    p.gk = pick_gk(p.K);
-    const size_t smem = gemm2_smem_bytes(p.K, p.N, static_cast<size_t>(p.gk) * (p.bn / cs) * 128, p.stages, rowblock);
+    const size_t smem = gemm2_smem_bytes(p.K, p.N, p.bn / cs, p.stages, rowblock);
     if (smem > 227 * 1024) return fail(DDC_E_INVALID, "gemm: %zu B of shared memory needed", smem);
     p.num_tiles = ((p.M + G2_BM - 1) / G2_BM + cs - 1) / cs * cs;
     if (f16) {
@@ -435,22 +405,19 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
         if (r == DDC_OK) r = make_tmap(m, f32, base, rows, cols, box);
     };
     pl->maps_B = 0;
-    auto mko = [&](CUtensorMap* m, const void* base, uint64_t rows, uint64_t K, uint32_t box) {
-        if (r == DDC_OK) r = make_tmap_operand(m, base, rows, K, box, pick_gk(static_cast<int>(K)));
-    };
-    mko(&pl->tm_Ap, pl->Ap, Mp, pl->Kp, G2_BM);
-    mko(&pl->tm_O, pl->O, Mp, C, G2_BM);
-    mko(&pl->tm_Hd, pl->Hd, Mp, C, G2_BM);
-    mko(&pl->tm_XN, pl->XN, Mp, C, G2_BM);
+    mk(&pl->tm_Ap, false, pl->Ap, Mp, pl->Kp, G2_BM);
+    mk(&pl->tm_O, false, pl->O, Mp, C, G2_BM);
+    mk(&pl->tm_Hd, false, pl->Hd, Mp, C, G2_BM);
+    mk(&pl->tm_XN, false, pl->XN, Mp, C, G2_BM);
     mk(&pl->tm_Xld, true, pl->X, Mp, C, 32);
     for (int cs = 1; cs <= 2; ++cs) {
-        mko(&pl->tm_wpatch[cs - 1], pl->w_patch, C, pl->Kp, pl->bn_row / cs);
-        mko(&pl->tm_whead[cs - 1], pl->w_head, pl->P, C, pl->bn_head / cs);
+        mk(&pl->tm_wpatch[cs - 1], false, pl->w_patch, C, pl->Kp, pl->bn_row / cs);
+        mk(&pl->tm_whead[cs - 1], false, pl->w_head, pl->P, C, pl->bn_head / cs);
         for (auto& l : pl->layers) {
-            mko(&l.tm_qkv[cs - 1], l.w_qkv, 3 * C, C, pl->bn_qkv / cs);
-            mko(&l.tm_proj[cs - 1], l.w_proj, C, C, pl->bn_row / cs);
-            mko(&l.tm_fc1[cs - 1], l.w_fc1, C, C, pl->bn_fc1 / cs);
-            mko(&l.tm_fc2[cs - 1], l.w_fc2, C, C, pl->bn_row / cs);
+            mk(&l.tm_qkv[cs - 1], false, l.w_qkv, 3 * C, C, pl->bn_qkv / cs);
+            mk(&l.tm_proj[cs - 1], false, l.w_proj, C, C, pl->bn_row / cs);
+            mk(&l.tm_fc1[cs - 1], false, l.w_fc1, C, C, pl->bn_fc1 / cs);
+            mk(&l.tm_fc2[cs - 1], false, l.w_fc2, C, C, pl->bn_row / cs);
         }
     }
     if (r != DDC_OK) {
@@ -812,8 +779,8 @@ extern "C" int ddc_k_gemm(int32_t fmt, int32_t epi, int32_t M, int32_t N, int32_
     const int bn = (epi == S_F32) ? pick_bn_f32(N) : pick_bn_stream(N);
     if (bn == 0) return fail(DDC_E_INVALID, "N=%d must be a multiple of %d", N, epi == S_F32 ? 16 : 64);
     CUtensorMap tmA, tmB, tmO;
-    TRY(make_tmap_operand(&tmA, A, Mp, K, G2_BM, pick_gk(K)));
-    TRY(make_tmap_operand(&tmB, W, N, K, bn / cs, pick_gk(K)));
+    TRY(make_tmap(&tmA, false, A, Mp, K, G2_BM));
+    TRY(make_tmap(&tmB, false, W, N, K, bn / cs));
     Gemm2Params p{};
     p.M = M; p.N = N; p.K = K; p.bn = bn; p.stages = pick_stages2(K, N, bn / cs, false); p.bias = bias;
     switch (epi) {
@@ -840,9 +807,9 @@ extern "C" int ddc_k_gemm_resid_ln(int32_t fmt, int32_t M, int32_t C, int32_t K,
     const uint64_t Mp = (static_cast<uint64_t>(M) + G2_BM - 1) / G2_BM * G2_BM;
     const int bn = pick_bn_row(C);
     CUtensorMap tmA, tmB, tmO, tmR, tmN;
-    TRY(make_tmap_operand(&tmA, A, Mp, K, G2_BM, pick_gk(K)));
+    TRY(make_tmap(&tmA, false, A, Mp, K, G2_BM));
     const int cs = gemm_cluster_size(M);
-    TRY(make_tmap_operand(&tmB, W, C, K, bn / cs, pick_gk(K)));
+    TRY(make_tmap(&tmB, false, W, C, K, bn / cs));
     TRY(make_tmap(&tmO, true, x, M, C, 32));
     TRY(make_tmap(&tmR, true, x, Mp, C, 32));
     TRY(make_tmap(&tmN, false, xn, M, C, 32));

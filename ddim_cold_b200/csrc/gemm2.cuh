@@ -45,7 +45,6 @@ constexpr int G2_TAIL_BYTES = 3072;         // barriers, TMEM slot, row-statisti
 
 struct Gemm2Params {
     int M, N, K, bn, stages, num_tiles;
-    int gk;                  // K blocks fetched per TMA instruction / per ring stage (divides K/64)
     const float* bias;
     float* out_f32;          // S_F32
     int ld_f32;
@@ -76,9 +75,8 @@ __host__ __device__ inline uint32_t g2_pow2_cols(uint32_t c) {
 // given to shared memory there is no L1 left, and a per-chunk __ldg would pay an L2 round trip.
 __host__ __device__ inline size_t gemm2_param_bytes(int N, bool rowblock) { return static_cast<size_t>(rowblock ? 3 : 1) * N * 4; }
 
-// `stage_bytes` = this CTA's bytes per W ring stage = gk * (bn / CS) * 128
-inline size_t gemm2_smem_bytes(int K, int N, size_t stage_bytes, int stages, bool rowblock) {
-    return 1024 + static_cast<size_t>(K / G2_BK) * G2_A_KB_BYTES + static_cast<size_t>(stages) * stage_bytes +
+inline size_t gemm2_smem_bytes(int K, int N, int bn, int stages, bool rowblock) {
+    return 1024 + static_cast<size_t>(K / G2_BK) * G2_A_KB_BYTES + static_cast<size_t>(stages) * bn * 128 +
            static_cast<size_t>(G2_EPI_WARPS) * (rowblock ? G2_ES_ROW : G2_ES_STREAM) * G2_SLOT_BYTES +
            ((gemm2_param_bytes(N, rowblock) + 127) & ~static_cast<size_t>(127)) + G2_TAIL_BYTES;
 }
@@ -103,9 +101,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
     const int kblocks = p.K / G2_BK;
     const int num_nt = p.N / p.bn;
-    const int groups = kblocks / p.gk;                                       // TMA loads per operand tile
-    const uint32_t b_kb_bytes = static_cast<uint32_t>(p.bn / CS) * 128u;    // this CTA's share of one W K block
-    const uint32_t b_stage_bytes = b_kb_bytes * static_cast<uint32_t>(p.gk);
+    const uint32_t b_stage_bytes = static_cast<uint32_t>(p.bn / CS) * 128u;   // this CTA's share of a W tile
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem_a + static_cast<size_t>(kblocks) * G2_A_KB_BYTES;
     uint8_t* smem_e = smem_b + static_cast<size_t>(p.stages) * b_stage_bytes;
@@ -117,9 +113,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     uint64_t* afull_bar = bars + 16;       // [8]  A K-block landed
     uint64_t* aempty_bar = bars + 24;      // [8]  A K-block no longer needed by this tile
     uint64_t* tfull_bar = bars + 32;       // [4]  accumulator stage / N tile complete
-    uint64_t* tempty_bar = bars + 36;      // [4]  accumulator stage drained
-    uint64_t* res_bar = bars + 40;         // [16] residual chunk landed (per epilogue warp x slot)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 56);
+    uint64_t* tempty_bar = bars + 36;      // [2]  accumulator drained
+    uint64_t* res_bar = bars + 38;         // [16] residual chunk landed (per epilogue warp x slot)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 54);
     float* red = reinterpret_cast<float*>(bars + 64);     // [2 stats][2 halves][128 rows] partial row statistics
 
     const int warp = threadIdx.x >> 5;
@@ -130,11 +126,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const int first_tile = static_cast<int>((blockIdx.x / CS) * CS + crank);
     const int tile_step = gridDim.x;
     const bool leader = crank == 0;
-    // stream flavour: as many accumulator stages as the 512 TMEM columns hold (max 4), so the MMA issuer can
-    // run several N tiles ahead of the epilogue and the drain handshake is off the critical path
     const uint32_t acc_stride = g2_pow2_cols(p.bn);
-    const uint32_t nacc = (512u / acc_stride) < 4u ? (512u / acc_stride) : 4u;
-    const uint32_t tmem_cols = ROWBLOCK ? g2_pow2_cols(p.N) : g2_pow2_cols(nacc * acc_stride);
+    const uint32_t tmem_cols = ROWBLOCK ? g2_pow2_cols(p.N) : g2_pow2_cols(2 * acc_stride);
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -149,7 +142,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             mbar_init(&aempty_bar[i], 1);
         }
         for (int i = 0; i < 4; ++i) mbar_init(&tfull_bar[i], 1);
-        for (int i = 0; i < 4; ++i) mbar_init(&tempty_bar[i], G2_EPI_WARPS * CS);   // both CTAs' epilogue warps
+        mbar_init(&tempty_bar[0], G2_EPI_WARPS * CS);     // the leader hears from both CTAs' epilogue warps
+        mbar_init(&tempty_bar[1], G2_EPI_WARPS * CS);
         for (int i = 0; i < 16; ++i) mbar_init(&res_bar[i], 1);
         fence_barrier_init();
     }
@@ -174,46 +168,38 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
     if (warp == 0) {
         // ================================================================= TMA producer
-        // every lane runs the loop (waits included); one elected lane issues, with warp-uniform operands so
-        // that ptxas emits the TMA instructions without a per-instruction leader-election sequence
-        uint32_t stage = 0, phase = 0, tcount = 0;
-        for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
-            const int m0 = tile * G2_BM;
-            for (int g = 0; g < groups; ++g) {
-                mbar_wait(&aempty_bar[g], (tcount & 1) ^ 1);
-                if (elect_one()) {
-                    uint8_t* dst = smem_a + static_cast<size_t>(g) * p.gk * G2_A_KB_BYTES;
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0, tcount = 0;
+            for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
+                const int m0 = tile * G2_BM;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    mbar_wait(&aempty_bar[kb], (tcount & 1) ^ 1);
                     if (CS == 1) {
-                        mbar_arrive_expect_tx(&afull_bar[g], p.gk * G2_A_KB_BYTES);
-                        tma_load_3d(dst, &tmA, &afull_bar[g], 0, m0, g * p.gk);
+                        mbar_arrive_expect_tx(&afull_bar[kb], G2_A_KB_BYTES);
+                        tma_load_2d(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0);
                     } else {      // both CTAs' bytes are credited to the leader's barrier
-                        if (leader) mbar_arrive_expect_tx(&afull_bar[g], CS * p.gk * G2_A_KB_BYTES);
-                        tma_load_3d_pair(dst, &tmA, &afull_bar[g], 0, m0, g * p.gk);
+                        if (leader) mbar_arrive_expect_tx(&afull_bar[kb], CS * G2_A_KB_BYTES);
+                        tma_load_2d_pair(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0);
                     }
                 }
-                __syncwarp();
-            }
-            if (lane == 0) g2_stamp(p, 0, tcount * 8);
-            for (int nt = 0; nt < num_nt; ++nt) {
-                if (nt > 0 && lane == 0) g2_stamp(p, 0, tcount * 8 + nt);
-                const int brow = nt * p.bn + static_cast<int>(crank) * (p.bn / CS);   // this CTA's rows of the W tile
-                for (int g = 0; g < groups; ++g) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
-                    if (elect_one()) {
-                        uint8_t* dst = smem_b + static_cast<size_t>(stage) * b_stage_bytes;
+                for (int nt = 0; nt < num_nt; ++nt) {
+                    for (int kb = 0; kb < kblocks; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
                         if (CS == 1) {
                             mbar_arrive_expect_tx(&full_bar[stage], b_stage_bytes);
-                            tma_load_3d(dst, &tmB, &full_bar[stage], 0, brow, g * p.gk);
-                        } else {
+                            tma_load_2d(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
+                                        kb * G2_BK, nt * p.bn);
+                        } else {      // this CTA stages rows [crank*bn/2, +bn/2) of the W tile
                             if (leader) mbar_arrive_expect_tx(&full_bar[stage], CS * b_stage_bytes);
-                            tma_load_3d_pair(dst, &tmB, &full_bar[stage], 0, brow, g * p.gk);
+                            tma_load_2d_pair(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
+                                             kb * G2_BK, nt * p.bn + static_cast<int>(crank) * (p.bn / CS));
                         }
+                        if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
                     }
-                    __syncwarp();
-                    if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
                 }
             }
         }
+        __syncwarp();
     } else if (warp == 1 && leader) {
         // ================================================================= MMA issuer (pair leader only)
         const uint32_t idesc = umma_idesc_16bit(G2_BM * CS, static_cast<uint32_t>(p.bn), F16);
@@ -221,7 +207,6 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         const uint64_t ad0 = umma_desc_sw128(smem_u32(smem_a));
         const uint64_t bd0 = umma_desc_sw128(smem_u32(smem_b));
         const uint32_t b_stage_units = b_stage_bytes >> 4;
-        const uint32_t b_kb_units = b_kb_bytes >> 4;
         uint32_t stage = 0, phase = 0, tcount = 0, acc_it = 0;
         for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
             for (int nt = 0; nt < num_nt; ++nt) {
@@ -232,39 +217,33 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     d_tmem = tb + static_cast<uint32_t>(nt * p.bn);
                     done_bar = &tfull_bar[nt];
                 } else {
-                    const uint32_t acc = acc_it % nacc;
-                    mbar_wait(&tempty_bar[acc], ((acc_it / nacc) & 1) ^ 1);
+                    const uint32_t acc = acc_it & 1;
+                    mbar_wait(&tempty_bar[acc], ((acc_it >> 1) & 1) ^ 1);
                     d_tmem = tb + acc * acc_stride;
                     done_bar = &tfull_bar[acc];
                     ++acc_it;
                 }
                 tc_fence_after();
-                if (lane == 0) g2_stamp(p, 1, (tcount * 8 + nt) * 2);
-                for (int g = 0; g < groups; ++g) {
-                    if (nt == 0) mbar_wait(&afull_bar[g], tcount & 1);
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    if (nt == 0) mbar_wait(&afull_bar[kb], tcount & 1);
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     if (elect_one()) {
-                        for (int j = 0; j < p.gk; ++j) {
-                            const int kb = g * p.gk + j;
-                            umma_kblock<CS>(d_tmem, ad0 + static_cast<uint64_t>(kb * (G2_A_KB_BYTES >> 4)),
-                                            bd0 + static_cast<uint64_t>(stage * b_stage_units + j * b_kb_units), idesc,
-                                            kb != 0 ? 1u : 0u);
-                        }
+                        umma_kblock<CS>(d_tmem, ad0 + static_cast<uint64_t>(kb * (G2_A_KB_BYTES >> 4)),
+                                        bd0 + static_cast<uint64_t>(stage * b_stage_units), idesc, kb != 0 ? 1u : 0u);
                         if (CS == 1) {
                             umma_commit(&empty_bar[stage]);
-                            if (nt == num_nt - 1) umma_commit(&aempty_bar[g]);
-                            if (g == groups - 1) umma_commit(done_bar);
+                            if (nt == num_nt - 1) umma_commit(&aempty_bar[kb]);
+                            if (kb == kblocks - 1) umma_commit(done_bar);
                         } else {      // both CTAs' producers / epilogues are released
                             umma_commit_pair(&empty_bar[stage]);
-                            if (nt == num_nt - 1) umma_commit_pair(&aempty_bar[g]);
-                            if (g == groups - 1) umma_commit_pair(done_bar);
+                            if (nt == num_nt - 1) umma_commit_pair(&aempty_bar[kb]);
+                            if (kb == kblocks - 1) umma_commit_pair(done_bar);
                         }
                     }
                     __syncwarp();
                     if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
                 }
-                if (lane == 0) g2_stamp(p, 1, (tcount * 8 + nt) * 2 + 1);
             }
         }
     } else if (warp >= 4) {
@@ -284,10 +263,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 const int row0 = tile * G2_BM + q * 32;
                 const int row = row0 + lane;
                 for (int nt = 0; nt < num_nt; ++nt, ++acc_it) {
-                    const uint32_t acc = acc_it % nacc;
-                    mbar_wait(&tfull_bar[acc], (acc_it / nacc) & 1);
+                    const uint32_t acc = acc_it & 1;
+                    mbar_wait(&tfull_bar[acc], (acc_it >> 1) & 1);
                     tc_fence_after();
-                    if (warp == 4 && lane == 0) g2_stamp(p, 2, (tcount * 8 + nt) * 2);
                     const uint32_t t_row = lane_taddr + acc * acc_stride;
                     if (EPI == S_F32) {
                         for (int c = 16 * hf; c < p.bn; c += 32) {
@@ -344,7 +322,6 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     }
                     tc_fence_before();
                     __syncwarp();
-                    if (warp == 4 && lane == 0) g2_stamp(p, 2, (tcount * 8 + nt) * 2 + 1);
                     if (lane == 0) { if (CS == 1) mbar_arrive(&tempty_bar[acc]); else mbar_arrive_leader(&tempty_bar[acc]); }
                 }
             }
