@@ -46,6 +46,7 @@ SIGNATURES = {
     "ddc_plan_destroy": (C.c_int, [_vp]),
     "ddc_pack_weights": (C.c_int, [_vp, C.POINTER(_vp), _i32, _vp]),
     "ddc_forward": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp]),
+    "ddc_forward_fixed_scratch": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _vp]),
     "ddc_sample": (C.c_int, [_vp, _vp, _i32, C.POINTER(Step), _i32, _vp, _vp, _vp, _i32, _vp]),
     "ddc_launches_per_step": (C.c_int, [_vp]),
     "ddc_profile_steps": (C.c_int, [_vp, _vp, _i32, C.POINTER(Step), _i32, C.POINTER(C.c_float), C.POINTER(_i32), _vp]),

@@ -282,6 +282,20 @@ struct ddc_plan {
     // graph cache
     cudaGraphExec_t gexec;
     GraphKey gkey;
+    // ddc_forward_fixed_scratch: activation pointers / descriptors into the library's built-in array (plain
+    // members, so that entry point never touches the heap)
+    struct WorkView {
+        float* X;
+        bf16 *QKV, *O, *Hd, *Ap, *XN;
+        float* Y;
+        StepEntry* tbl;
+        int* ctr;
+        CUtensorMap tm_Ap, tm_O, tm_Hd, tm_XN, tm_Xld, st_QKV, st_Hd, st_XN, st_X;
+        int maps_B, Mpad, maxB;
+        cudaGraphExec_t gexec;
+    };
+    WorkView fixed_view;
+    int fixed_view_cap;              // images the fixed view was laid out for (0 = not built yet)
 };
 
 struct Carver {
@@ -393,6 +407,7 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
     pl->f16 = false;
     pl->gexec = nullptr;
     pl->gkey = GraphKey{0, nullptr, nullptr, nullptr, nullptr};
+    pl->fixed_view_cap = 0;
     size_t w = 0, k = 0;
     carve(pl, weight_arena, work_arena, &w, &k);
     if (w > weight_bytes || k > work_bytes) {
@@ -624,6 +639,120 @@ extern "C" int ddc_forward(ddc_plan* pl, const float* x, const int32_t* t, int32
     head_ddim_kernel<MODE_FORWARD><<<dim3(q.H / q.p, batch), 256, head_ddim_smem(pl->sh), st>>>(q);
     CK(cudaGetLastError());
     return DDC_OK;
+}
+
+// ------------------------------------------------------------------------------- forward without any allocation
+// Some hosts may not allocate device memory at the moment they need a prediction: a serving loop that has
+// handed its whole memory budget to another framework's pool, code between cudaStreamBeginCapture and
+// EndCapture (cudaMalloc is illegal there), or a latency-critical thread for which cudaMalloc's implicit
+// device synchronisation is unacceptable.  For them the activations of one forward pass can live in this
+// fixed array instead of a caller-provided work arena.  It is part of the library image: every GPU that
+// loads the library carries it until the process exits, which is why it is kept modest.
+#define DDC_FIXED_SCRATCH_BYTES (32u << 20)
+static __device__ __align__(256) unsigned char g_fixed_scratch[DDC_FIXED_SCRATCH_BYTES];
+static void* g_fixed_scratch_dev[64] = {nullptr};   // per device: the array's DEVICE address (the symbol itself is a
+                                                    // host-side stand-in and must never be handed to a kernel)
+
+static size_t fixed_scratch_layout(const ddc_plan* pl, int B, ddc_plan::WorkView* v, char* origin) {
+    const size_t C = pl->C, P = pl->P, Kp = pl->Kp;
+    const size_t Mp = (static_cast<size_t>(B) * pl->L + G2_BM - 1) / G2_BM * G2_BM;
+    Carver k{origin, 0};
+    float* X = k.take<float>(Mp * C);
+    bf16* QKV = k.take<bf16>(Mp * 3 * C);
+    bf16* O = k.take<bf16>(Mp * C);
+    bf16* Hd = k.take<bf16>(Mp * C);
+    bf16* Ap = k.take<bf16>(Mp * Kp);
+    bf16* XN = k.take<bf16>(Mp * C);
+    float* Y = k.take<float>(Mp * P);
+    if (v != nullptr) {
+        v->X = X; v->QKV = QKV; v->O = O; v->Hd = Hd; v->Ap = Ap; v->XN = XN; v->Y = Y;
+        v->tbl = nullptr; v->ctr = nullptr;
+        v->Mpad = static_cast<int>(Mp);
+        v->maxB = B;
+        v->maps_B = 0;
+        v->gexec = nullptr;
+    }
+    return (k.off + 255) & ~static_cast<size_t>(255);
+}
+
+static void view_save(const ddc_plan* pl, ddc_plan::WorkView* v) {
+    v->X = pl->X; v->QKV = pl->QKV; v->O = pl->O; v->Hd = pl->Hd; v->Ap = pl->Ap; v->XN = pl->XN; v->Y = pl->Y;
+    v->tbl = pl->tbl; v->ctr = pl->ctr;
+    v->tm_Ap = pl->tm_Ap; v->tm_O = pl->tm_O; v->tm_Hd = pl->tm_Hd; v->tm_XN = pl->tm_XN; v->tm_Xld = pl->tm_Xld;
+    v->st_QKV = pl->st_QKV; v->st_Hd = pl->st_Hd; v->st_XN = pl->st_XN; v->st_X = pl->st_X;
+    v->maps_B = pl->maps_B; v->Mpad = pl->Mpad; v->maxB = pl->maxB; v->gexec = pl->gexec;
+}
+
+static void view_install(ddc_plan* pl, const ddc_plan::WorkView* v) {
+    pl->X = v->X; pl->QKV = v->QKV; pl->O = v->O; pl->Hd = v->Hd; pl->Ap = v->Ap; pl->XN = v->XN; pl->Y = v->Y;
+    pl->tbl = v->tbl; pl->ctr = v->ctr;
+    pl->tm_Ap = v->tm_Ap; pl->tm_O = v->tm_O; pl->tm_Hd = v->tm_Hd; pl->tm_XN = v->tm_XN; pl->tm_Xld = v->tm_Xld;
+    pl->st_QKV = v->st_QKV; pl->st_Hd = v->st_Hd; pl->st_XN = v->st_XN; pl->st_X = v->st_X;
+    pl->maps_B = v->maps_B; pl->Mpad = v->Mpad; pl->maxB = v->maxB; pl->gexec = v->gexec;
+}
+
+extern "C" int ddc_forward_fixed_scratch(ddc_plan* pl, const float* x, const int32_t* t, int32_t batch, float* out,
+                                         void* stream) {
+    if (pl == nullptr) return fail(DDC_E_INVALID, "plan is NULL");
+    if (!pl->packed) return fail(DDC_E_STATE, "ddc_pack_weights has not been called on this plan");
+    if (x == nullptr || t == nullptr || out == nullptr) return fail(DDC_E_INVALID, "NULL tensor");
+    if (batch <= 0) return fail(DDC_E_INVALID, "batch %d", batch);
+    const size_t need = fixed_scratch_layout(pl, batch, nullptr, nullptr);
+    if (need > DDC_FIXED_SCRATCH_BYTES) {
+        int fit = batch;
+        while (fit > 0 && fixed_scratch_layout(pl, fit, nullptr, nullptr) > DDC_FIXED_SCRATCH_BYTES) fit -= (fit > 64 ? fit / 16 : 1);
+        while (fixed_scratch_layout(pl, fit + 1, nullptr, nullptr) <= DDC_FIXED_SCRATCH_BYTES) ++fit;
+        return fail(DDC_E_INVALID,
+                    "ddc_forward_fixed_scratch: batch %d needs %zu B of scratch but the built-in array holds %u B "
+                    "(at most %d images of this shape); use ddc_forward with a caller-provided work arena",
+                    batch, need, DDC_FIXED_SCRATCH_BYTES, fit);
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int dev = pl->device;
+    if (dev < 0 || dev >= 64) return fail(DDC_E_INVALID, "device %d", dev);
+    CK(cudaSetDevice(dev));
+    if (g_fixed_scratch_dev[dev] == nullptr) {
+        // first call on this device: resolve the symbol to its address ON THIS DEVICE (must happen with the
+        // device current, and outside stream capture)
+        void* ptr = nullptr;
+        CK(cudaGetSymbolAddress(&ptr, g_fixed_scratch));
+        if (ptr == nullptr) return fail(DDC_E_CUDA, "cudaGetSymbolAddress returned a null address");
+        g_fixed_scratch_dev[dev] = ptr;
+    }
+    if (pl->fixed_view_cap < batch) {
+        // lay the activations of as many images as fit out in the built-in array and describe them to the TMA
+        // unit: host-side bookkeeping inside the plan struct, no heap, no device memory
+        int fit = batch;
+        while (fixed_scratch_layout(pl, fit * 2, nullptr, nullptr) <= DDC_FIXED_SCRATCH_BYTES && fit < (1 << 20)) fit *= 2;
+        ddc_plan::WorkView v;
+        fixed_scratch_layout(pl, fit, &v, static_cast<char*>(g_fixed_scratch_dev[dev]));
+        const uint64_t C = pl->C, Mp = v.Mpad;
+        TRY(make_tmap(&v.tm_Ap, false, v.Ap, Mp, pl->Kp, G2_BM));
+        TRY(make_tmap(&v.tm_O, false, v.O, Mp, C, G2_BM));
+        TRY(make_tmap(&v.tm_Hd, false, v.Hd, Mp, C, G2_BM));
+        TRY(make_tmap(&v.tm_XN, false, v.XN, Mp, C, G2_BM));
+        TRY(make_tmap(&v.tm_Xld, true, v.X, Mp, C, 32));
+        pl->fixed_view = v;
+        pl->fixed_view_cap = fit;
+    }
+    // Run the ordinary kernel chain with the plan temporarily looking at the built-in array.  Nothing in the
+    // array has to start at zero: every row below batch*L of every buffer is written by the kernel that precedes
+    // its first reader, and rows above it are computed on but never stored.
+    ddc_plan::WorkView own;
+    view_save(pl, &own);
+    view_install(pl, &pl->fixed_view);
+    int rc = enqueue_predictor(pl, x, batch, t, false, st);
+    if (rc == DDC_OK) {
+        HeadDdimParams q{};
+        q.y = pl->Y; q.ldy = pl->P; q.x = out;
+        q.H = pl->sh.img_h; q.W = pl->sh.img_w; q.p = pl->sh.patch; q.L = pl->L; q.B = batch;
+        head_ddim_kernel<MODE_FORWARD><<<dim3(q.H / q.p, batch), 256, head_ddim_smem(pl->sh), st>>>(q);
+        const cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) rc = fail(DDC_E_CUDA, "head_ddim launch: %s", cudaGetErrorString(e));
+    }
+    view_save(pl, &pl->fixed_view);      // keeps the store descriptors built for this batch
+    view_install(pl, &own);
+    return rc;
 }
 
 static int enqueue_step(ddc_plan* pl, float* x, int B, float* x0_last, float* x0_seq, float* eps_seq, cudaStream_t st,

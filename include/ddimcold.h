@@ -98,6 +98,26 @@ int ddc_pack_weights(ddc_plan* plan, const float* const* tensors, int32_t n_tens
  * (reference ViT.py:208-218).  x, out: [B,3,H,W] fp32; t: [B] int32 on the device. */
 int ddc_forward(ddc_plan* plan, const float* x, const int32_t* t, int32_t batch, float* out, void* stream);
 
+/* ddc_forward for callers that cannot allocate device memory (no counterpart in the reference).
+ * Same inputs, outputs and result as ddc_forward, but the intermediate activations live in a fixed
+ * 32 MiB device array that is part of this library instead of the plan's work arena, so the call
+ * performs no cudaMalloc / cudaFree and needs no extra arena from the host.  Meant for hosts whose
+ * device memory is owned by another allocator (a serving process that gave its whole budget to a
+ * framework pool), for latency-critical threads that must not hit cudaMalloc's implicit device
+ * synchronisation, and for code that is not allowed to allocate at that point of its lifetime.
+ *   - Limit: the activations of `batch` images must fit in 32 MiB (about 64 images of the S1 shape,
+ *     a few thousand of a 16x16 toy shape); larger batches fail with DDC_E_INVALID and a message
+ *     naming the largest batch that fits.
+ *   - The first call on each device resolves the array's device address (cudaGetSymbolAddress) and
+ *     builds host-side descriptors; make that first call before any stream capture begins.
+ *   - The array is shared by every plan and every call on that device and keeps the previous call's
+ *     contents.  A forward pass overwrites everything it later reads, so nothing needs clearing,
+ *     but two calls that overlap on the GPU (different streams, or another process thread) race on
+ *     it: serialise them.
+ *   - Every GPU that loads the library holds the 32 MiB until the process exits. */
+int ddc_forward_fixed_scratch(ddc_plan* plan, const float* x, const int32_t* t, int32_t batch, float* out,
+                              void* stream);
+
 /* The whole sampling loop (reference ViT.py:226-236): for each table entry run the predictor
  * at entry.t, clamp to [-1,1], apply the DDIM update in place on `x`.
  *   x        [B,3,H,W] fp32, in: x_T (or the partially noised draft), out: the final state
