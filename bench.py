@@ -239,17 +239,19 @@ def main():
     with contextlib.redirect_stdout(sys.stderr):       # the sampler prints a progress line like the reference
         for _ in range(2):
             model.sampler(dev, k, B, noise=x_host)
+    e2e_out = torch.empty((B * world, 3, H, H), dtype=torch.float32).pin_memory() if (world > 1 and rank == 0) else None
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         with contextlib.redirect_stdout(sys.stderr):
-            img = model.sampler(dev, k, B, noise=x_host)
-        if world > 1:                                  # the one NCCL call: final gather of the images
-            g = img.to(dev, non_blocking=True)
-            bufs = [torch.empty_like(g) for _ in range(world)] if rank == 0 else None
-            dist.gather(g, bufs, dst=0)
+            img = model.sampler(dev, k, B, noise=x_host, return_on_device=world > 1)
+        if world > 1:                                  # the one NCCL call: final gather of the images, then one D2H
+            bufs = [torch.empty_like(img) for _ in range(world)] if rank == 0 else None
+            dist.gather(img, bufs, dst=0)
             if rank == 0:
-                img = torch.cat(bufs).cpu()
+                for r_, b_ in enumerate(bufs):
+                    e2e_out[r_ * B:(r_ + 1) * B].copy_(b_, non_blocking=True)
+                torch.cuda.synchronize(dev)
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3
     print("", file=sys.stderr)
@@ -303,8 +305,9 @@ def main():
         "ms_per_denoise_step": dev_ms / args.steps / n_steps,
         "tensor_tflops_whole_loop_per_gpu": whole_tf,
         "tensor_frac_whole_loop": whole_tf / peak_tf,
-        "e2e": {"value": e2e_val, "unit": "images/s", "h2d_bytes_per_step": int(x_host.numel() * 4),
-                "d2h_bytes_per_step": int(x_host.numel() * 4), "ms_per_step": e2e_ms / args.steps},
+        "e2e": {"value": e2e_val, "unit": "images/s", "h2d_bytes_per_step": int(x_host.numel() * 4) * world,
+                "d2h_bytes_per_step": int(x_host.numel() * 4) * world, "ms_per_step": e2e_ms / args.steps,
+                "note": "N>1: each rank uploads its own x_T; one NCCL gather to rank 0, which reads all images back"},
         "gpu_launches": launches_per_pass * args.steps,
         "clocks": clk,
         "roofline": {"bound": "tensor", "kernel": "gemm_umma_kernel<A_LN,EPI_BF16> (LayerNorm + qkv GEMM)",

@@ -25,20 +25,51 @@
 
 namespace ddc {
 
+// 2^x, one MUFU instruction (exp2f adds range fix-ups that softmax does not need; ex2(-inf) = +0)
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 constexpr int ATT_MAX_WARPS = 8;
 constexpr int ATT_GROUP_WARPS = 8;     // group kernel: one warp per 16-query tile, each walking the G heads
 
 // One 16-query tile against all keys of one head.  Ks/Vs point at the head's first column in
 // shared memory, RS is the row pitch in bytes, keys >= L are masked, rows [L, lk_pad) must be
 // zero.  On return o holds the normalised output fragments.
-template <int D, int KC, bool F16>
+// SWZ = false: rows of PITCH bytes, Ks/Vs already offset to the head's first column (cbase = 0).
+// SWZ = true : Ks/Vs are [rows x 128 B] tiles in the TMA 128-byte swizzle (PITCH = 128); `cbase` is the head's
+//              first 16-byte chunk inside the 128-byte row.
+// All ldmatrix row offsets are multiples of 8 plus (lane & 7), so the swizzle term (chunk ^ (row & 7)) is a
+// per-lane constant: addresses are one add away from a base computed once per tile.
+template <bool SWZ>
+__device__ __forceinline__ uint32_t att_addr(const uint8_t* base, int row, int chunk, int RS) {
+    return SWZ ? smem_u32(base + row * 128 + ((chunk ^ (row & 7)) << 4)) : smem_u32(base + row * RS + (chunk << 4));
+}
+
+template <int D, int KC, bool F16, bool SWZ, int PITCH>
 __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], const uint8_t* Ks, const uint8_t* Vs,
-                                             int RS, int L, int lk_pad, float scale_log2e, int lane,
-                                             float (&o)[D / 8][4]) {
+                                             int L, int lk_pad, float scale_log2e, int lane,
+                                             float (&o)[D / 8][4], int cbase = 0) {
     constexpr int NT = KC / 8;    // score n-tiles per key chunk
     constexpr int DT = D / 8;     // output n-tiles
     constexpr int DK = D / 16;    // k-steps of q k^T
     const int t = lane & 3;
+    const int l7 = lane & 7;
+    const uint32_t kbase = smem_u32(Ks) + static_cast<uint32_t>((l7 + ((lane >> 4) << 3)) * PITCH);
+    const uint32_t vbase = smem_u32(Vs) + static_cast<uint32_t>((l7 + (((lane >> 3) & 1) << 3)) * PITCH);
+    uint32_t kx[DK], vx[DT / 2];
+#pragma unroll
+    for (int ks = 0; ks < DK; ++ks) {
+        const int chunk = cbase + ks * 2 + ((lane >> 3) & 1);
+        kx[ks] = static_cast<uint32_t>((SWZ ? (chunk ^ l7) : chunk) << 4);
+    }
+#pragma unroll
+    for (int d2 = 0; d2 < DT / 2; ++d2) {
+        const int chunk = cbase + d2 * 2 + (lane >> 4);
+        vx[d2] = static_cast<uint32_t>((SWZ ? (chunk ^ l7) : chunk) << 4);
+    }
 #pragma unroll
     for (int i = 0; i < DT; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
     float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
@@ -51,21 +82,23 @@ __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], co
 #pragma unroll
             for (int ks = 0; ks < DK; ++ks) {
                 uint32_t b0, b1, b2, b3;
-                const int krow = kc0 + nt * 8 + (lane & 7) + ((lane >> 4) << 3);
-                const int kcol = ks * 16 + (((lane >> 3) & 1) << 3);
-                ldmatrix_x4(b0, b1, b2, b3, smem_u32(Ks + krow * RS + kcol * 2));
+                ldmatrix_x4(b0, b1, b2, b3, kbase + static_cast<uint32_t>((kc0 + nt * 8) * PITCH) + kx[ks]);
                 mma_16816<F16>(s[nt], qa[ks], b0, b1);
                 mma_16816<F16>(s[nt + 1], qa[ks], b2, b3);
             }
         }
-        float mx0 = m0, mx1 = m1;
+        // mask only the n-tiles that reach past the last key (raw scores; the scale is folded into the exponent)
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
-            const int key = kc0 + nt * 8 + 2 * t;
-            s[nt][0] = key < L ? s[nt][0] * scale_log2e : -INFINITY;
-            s[nt][1] = key + 1 < L ? s[nt][1] * scale_log2e : -INFINITY;
-            s[nt][2] = key < L ? s[nt][2] * scale_log2e : -INFINITY;
-            s[nt][3] = key + 1 < L ? s[nt][3] * scale_log2e : -INFINITY;
+            if (kc0 + nt * 8 + 8 > L) {
+                const int key = kc0 + nt * 8 + 2 * t;
+                if (key >= L) { s[nt][0] = -INFINITY; s[nt][2] = -INFINITY; }
+                if (key + 1 >= L) { s[nt][1] = -INFINITY; s[nt][3] = -INFINITY; }
+            }
+        }
+        float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
             mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
             mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
         }
@@ -73,15 +106,19 @@ __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], co
         mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
         mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
         mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-        const float c0 = exp2f(m0 - mx0), c1 = exp2f(m1 - mx1);
+        mx0 = fmaxf(m0, mx0 * scale_log2e);       // running max in the scaled (log2) domain; scale > 0
+        mx1 = fmaxf(m1, mx1 * scale_log2e);
+        const float c0 = ex2_approx(m0 - mx0), c1 = ex2_approx(m1 - mx1);
         m0 = mx0; m1 = mx1;
         l0 *= c0; l1 *= c1;
 #pragma unroll
         for (int i = 0; i < DT; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
-            s[nt][0] = exp2f(s[nt][0] - m0); s[nt][1] = exp2f(s[nt][1] - m0);
-            s[nt][2] = exp2f(s[nt][2] - m1); s[nt][3] = exp2f(s[nt][3] - m1);
+            s[nt][0] = ex2_approx(fmaf(s[nt][0], scale_log2e, -m0));
+            s[nt][1] = ex2_approx(fmaf(s[nt][1], scale_log2e, -m0));
+            s[nt][2] = ex2_approx(fmaf(s[nt][2], scale_log2e, -m1));
+            s[nt][3] = ex2_approx(fmaf(s[nt][3], scale_log2e, -m1));
             l0 += s[nt][0] + s[nt][1];
             l1 += s[nt][2] + s[nt][3];
         }
@@ -95,9 +132,7 @@ __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], co
 #pragma unroll
             for (int dt = 0; dt < DT; dt += 2) {
                 uint32_t b0, b1, b2, b3;
-                const int vrow = kc0 + kk * 16 + (lane & 7) + (((lane >> 3) & 1) << 3);
-                const int vcol = dt * 8 + ((lane >> 4) << 3);
-                ldmatrix_x4_trans(b0, b1, b2, b3, smem_u32(Vs + vrow * RS + vcol * 2));
+                ldmatrix_x4_trans(b0, b1, b2, b3, vbase + static_cast<uint32_t>((kc0 + kk * 16) * PITCH) + vx[dt / 2]);
                 mma_16816<F16>(o[dt], pa, b0, b1);
                 mma_16816<F16>(o[dt + 1], pa, b2, b3);
             }
@@ -168,7 +203,7 @@ attention_group_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int
             ldmatrix_x4(qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], smem_u32(qh + qrow * RS + qcol * 2));
         }
         float o[DT][4];
-        attend_qtile<D, KC, F16>(qa, Ks + head * D * 2, Vs + head * D * 2, RS, L, lk_pad, scale_log2e, lane, o);
+        attend_qtile<D, KC, F16, false, RS>(qa, Ks + head * D * 2, Vs + head * D * 2, L, lk_pad, scale_log2e, lane, o);
         // this task is the only reader of its 16 x D patch of Qs: reuse it as the output stage
         __syncwarp();
 #pragma unroll
@@ -240,7 +275,7 @@ attention_head_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int 
             }
         }
         float o[DT][4];
-        attend_qtile<D, KC, F16>(qa, Ks, Vs, RS, L, lk_pad, scale_log2e, lane, o);
+        attend_qtile<D, KC, F16, false, RS>(qa, Ks, Vs, L, lk_pad, scale_log2e, lane, o);
         bf16* ob = out + static_cast<size_t>(img) * L * C + head * D;
 #pragma unroll
         for (int dt = 0; dt < DT; ++dt) {

@@ -217,7 +217,7 @@ class DiffusionVisionTransformer(nn.Module):
 
     # ------------------------------------------------------------------ loops
     def _run_loop(self, device, x_init_cpu: torch.Tensor, table, n_steps: int, want_seq: bool = False,
-                  want_eps: bool = False, use_graph: bool = True):
+                  want_eps: bool = False, use_graph: bool = True, keep_on_device: bool = False):
         """Run the table-driven loop on `device` for CPU initial states [N,3,H,W].
         Returns (x0_last_cpu, x0_seq_cpu | None, eps_seq_cpu | None)."""
         lib = _lib.load()
@@ -232,7 +232,10 @@ class DiffusionVisionTransformer(nn.Module):
         x_pin = x_init_cpu.contiguous().float()
         if not x_pin.is_pinned():
             x_pin = x_pin.pin_memory()
-        out = torch.empty((N,) + tuple(x_pin.shape[1:]), dtype=torch.float32).pin_memory()
+        if keep_on_device:
+            out = torch.empty((N,) + tuple(x_pin.shape[1:]), dtype=torch.float32, device=dev)
+        else:
+            out = torch.empty((N,) + tuple(x_pin.shape[1:]), dtype=torch.float32).pin_memory()
         seq = torch.empty((n_steps, N) + tuple(x_pin.shape[1:]), dtype=torch.float32) if want_seq else None
         eps = torch.empty((n_steps, N) + tuple(x_pin.shape[1:]), dtype=torch.float32) if want_eps else None
         t_h2d = t_gpu = 0.0
@@ -263,15 +266,16 @@ class DiffusionVisionTransformer(nn.Module):
         print(f"\rnoise level {last_t}  {time.time() - start_time:.2f}", end='')
 
     @torch.no_grad()
-    def sampler(self, device, k=10, N=128, noise=None):
+    def sampler(self, device, k=10, N=128, noise=None, return_on_device=False):
         """DDIM sampling (reference ViT.py:220-237): CPU fp32 [N,3,H,W] in [0,1], the last step's
         clamped x0 prediction.  The initial noise is drawn on the CPU from the global torch RNG
-        exactly like the reference unless `noise` ([N,3,H,W], CPU or CUDA) is given."""
+        exactly like the reference unless `noise` ([N,3,H,W], CPU or CUDA) is given.
+        `return_on_device=True` (extension) leaves the images on `device`, e.g. for an NCCL gather."""
         start_time = time.time()
         table, n = _lib.ddim_table(k, self.total_steps)
         noisy_img = torch.normal(0, 1, (N, 3, self.img_size[0], self.img_size[1])) if noise is None \
             else noise.detach().float().cpu()
-        x0, _, _ = self._run_loop(device, noisy_img, table, n)
+        x0, _, _ = self._run_loop(device, noisy_img, table, n, keep_on_device=return_on_device)
         self._print_progress(table[n - 1].t, start_time)
         return (x0 + 1) / 2
 
