@@ -48,7 +48,9 @@ __device__ __forceinline__ uint32_t att_addr(const uint8_t* base, int row, int c
     return SWZ ? smem_u32(base + row * 128 + ((chunk ^ (row & 7)) << 4)) : smem_u32(base + row * RS + (chunk << 4));
 }
 
-template <int D, int KC, bool F16, bool SWZ, int PITCH>
+// SINGLE: the whole key range is one chunk (L <= KC; att_pick_kc then guarantees L > KC - 16), so only the last
+// two n-tiles can reach past L and the mask is resolved at compile time for all the others.
+template <int D, int KC, bool F16, bool SWZ, int PITCH, bool SINGLE>
 __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], const uint8_t* Ks, const uint8_t* Vs,
                                              int L, int lk_pad, float scale_log2e, int lane,
                                              float (&o)[D / 8][4], int cbase = 0) {
@@ -72,7 +74,10 @@ __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], co
     }
 #pragma unroll
     for (int i = 0; i < DT; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
-    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    // row sums ride on the tensor cores: P times a column of ones (every lane then holds its rows' sums)
+    constexpr uint32_t kOnes = F16 ? 0x3C003C00u : 0x3F803F80u;
+    float lsum[4] = {0.f, 0.f, 0.f, 0.f};
+    float m0 = -INFINITY, m1 = -INFINITY;
     for (int kc0 = 0; kc0 < lk_pad; kc0 += KC) {
         float s[NT][4];
 #pragma unroll
@@ -88,9 +93,16 @@ __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], co
             }
         }
         // mask only the n-tiles that reach past the last key (raw scores; the scale is folded into the exponent)
+        if (SINGLE) {
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt) {
-            if (kc0 + nt * 8 + 8 > L) {
+            for (int nt = (NT >= 2 ? NT - 2 : 0); nt < NT; ++nt) {
+                const int key = nt * 8 + 2 * t;
+                if (key >= L) { s[nt][0] = -INFINITY; s[nt][2] = -INFINITY; }
+                if (key + 1 >= L) { s[nt][1] = -INFINITY; s[nt][3] = -INFINITY; }
+            }
+        } else if (kc0 + KC > L) {          // only the last chunk reaches past L
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
                 const int key = kc0 + nt * 8 + 2 * t;
                 if (key >= L) { s[nt][0] = -INFINITY; s[nt][2] = -INFINITY; }
                 if (key + 1 >= L) { s[nt][1] = -INFINITY; s[nt][3] = -INFINITY; }
@@ -110,17 +122,17 @@ __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], co
         mx1 = fmaxf(m1, mx1 * scale_log2e);
         const float c0 = ex2_approx(m0 - mx0), c1 = ex2_approx(m1 - mx1);
         m0 = mx0; m1 = mx1;
-        l0 *= c0; l1 *= c1;
+        if (!SINGLE) {
+            lsum[0] *= c0; lsum[2] *= c1;
 #pragma unroll
-        for (int i = 0; i < DT; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+            for (int i = 0; i < DT; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+        }
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
             s[nt][0] = ex2_approx(fmaf(s[nt][0], scale_log2e, -m0));
             s[nt][1] = ex2_approx(fmaf(s[nt][1], scale_log2e, -m0));
             s[nt][2] = ex2_approx(fmaf(s[nt][2], scale_log2e, -m1));
             s[nt][3] = ex2_approx(fmaf(s[nt][3], scale_log2e, -m1));
-            l0 += s[nt][0] + s[nt][1];
-            l1 += s[nt][2] + s[nt][3];
         }
 #pragma unroll
         for (int kk = 0; kk < KC / 16; ++kk) {
@@ -129,6 +141,7 @@ __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], co
             pa[1] = pack2<F16>(s[2 * kk][2], s[2 * kk][3]);
             pa[2] = pack2<F16>(s[2 * kk + 1][0], s[2 * kk + 1][1]);
             pa[3] = pack2<F16>(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+            mma_16816<F16>(lsum, pa, kOnes, kOnes);
 #pragma unroll
             for (int dt = 0; dt < DT; dt += 2) {
                 uint32_t b0, b1, b2, b3;
@@ -138,86 +151,81 @@ __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], co
             }
         }
     }
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-    const float i0 = 1.f / l0, i1 = 1.f / l1;
+    const float i0 = 1.f / lsum[0], i1 = 1.f / lsum[2];
 #pragma unroll
     for (int i = 0; i < DT; ++i) { o[i][0] *= i0; o[i][1] *= i0; o[i][2] *= i1; o[i][3] *= i1; }
 }
 
 // ---------------------------------------------------------------------------- one CTA per (image, G heads)
-inline size_t att_group_smem_bytes(int L, int D, int KC, int G) {
-    const int lq = (L + 15) / 16 * 16;
+// Q, K and V column slices (G heads = 128 qkv columns) arrive as six [lk_pad x 64] TMA boxes in the 128-byte
+// swizzle behind one mbarrier -- no per-thread copy loop.  Rows [L, lk_pad) of a box belong to the next image
+// (or are zero-filled past the end): finite, and masked as keys.
+inline size_t att_group_smem_bytes(int L, int KC) {
     const int lk = (L + KC - 1) / KC * KC;
-    return static_cast<size_t>(lq + 2 * lk) * (G * D * 2 + 16);
+    return 1024 + static_cast<size_t>(6) * lk * 128 + 64;
 }
 
 template <int D, int KC, bool F16>
 __global__ void __launch_bounds__(ATT_GROUP_WARPS * 32, 2)
-attention_group_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int L, int C, float scale_log2e) {
-    extern __shared__ __align__(16) uint8_t att_smem[];
+attention_group_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ out, int L, int C,
+                       float scale_log2e) {
+    extern __shared__ uint8_t att_raw[];
     constexpr int G = 128 / D;            // heads per CTA
-    constexpr int W16 = G * D / 8;        // 16-byte chunks per token slice (16)
-    constexpr int RS = G * D * 2 + 16;    // +16 B pad keeps ldmatrix conflict-free
     constexpr int DK = D / 16, DT = D / 8;
+    const uint32_t ra = smem_u32(att_raw);
+    uint8_t* sm = att_raw + (((ra + 1023u) & ~1023u) - ra);
     const int hg = blockIdx.x, img = blockIdx.y;
     const int qtiles = (L + 15) / 16;
-    const int lq_pad = qtiles * 16;
-    const int lk_pad = (L + KC - 1) / KC * KC;
-    uint8_t* Qs = att_smem;
-    uint8_t* Ks = Qs + static_cast<size_t>(lq_pad) * RS;
-    uint8_t* Vs = Ks + static_cast<size_t>(lk_pad) * RS;
+    const int lk_pad = (L + KC - 1) / KC * KC;      // == box rows (single key chunk: L <= KC)
+    const uint32_t tile_bytes = static_cast<uint32_t>(lk_pad) * 128u;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(sm + 6 * tile_bytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nwarps = blockDim.x >> 5;
-    const size_t ld = static_cast<size_t>(3) * C;
-    const bf16* base = qkv + static_cast<size_t>(img) * L * ld + hg * (G * D);
-
-    for (int i = threadIdx.x; i < lk_pad * W16; i += blockDim.x) {
-        const int r = i / W16, c = i - r * W16;
-        if (r < L) {
-            const bf16* src = base + r * ld + c * 8;
-            if (r < lq_pad) cp_async16(smem_u32(Qs + r * RS + c * 16), src);
-            cp_async16(smem_u32(Ks + r * RS + c * 16), src + C);
-            cp_async16(smem_u32(Vs + r * RS + c * 16), src + 2 * C);
-        } else {
-            if (r < lq_pad) *reinterpret_cast<uint4*>(Qs + r * RS + c * 16) = make_uint4(0, 0, 0, 0);
-            *reinterpret_cast<uint4*>(Ks + r * RS + c * 16) = make_uint4(0, 0, 0, 0);
-            *reinterpret_cast<uint4*>(Vs + r * RS + c * 16) = make_uint4(0, 0, 0, 0);
-        }
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        fence_barrier_init();
+        mbar_arrive_expect_tx(bar, 6 * tile_bytes);
+#pragma unroll
+        for (int m = 0; m < 3; ++m)
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                tma_load_2d(sm + (m * 2 + h) * tile_bytes, &tmQKV, bar, m * C + hg * 128 + h * 64, img * L);
     }
-    cp_async_wait_all();
     __syncthreads();
+    mbar_wait(bar, 0);
 
     const int g = lane >> 2, t = lane & 3;
     for (int task = warp; task < G * qtiles; task += nwarps) {
         const int head = task % G;
         const int q0 = (task / G) * 16;
-        uint8_t* qh = Qs + head * D * 2;
+        const int half = (head * D) / 64;                 // which 64-column box
+        const int cbase = ((head * D) % 64) / 8;          // first 16-byte chunk of this head in the 128-byte row
+        uint8_t* Qt = sm + (0 * 2 + half) * tile_bytes;
+        const uint8_t* Kt = sm + (1 * 2 + half) * tile_bytes;
+        const uint8_t* Vt = sm + (2 * 2 + half) * tile_bytes;
         uint32_t qa[DK][4];
 #pragma unroll
         for (int ks = 0; ks < DK; ++ks) {
             const int qrow = q0 + (lane & 7) + (((lane >> 3) & 1) << 3);
-            const int qcol = ks * 16 + ((lane >> 4) << 3);
-            ldmatrix_x4(qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], smem_u32(qh + qrow * RS + qcol * 2));
+            ldmatrix_x4(qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], att_addr<true>(Qt, qrow, cbase + ks * 2 + (lane >> 4), 0));
         }
         float o[DT][4];
-        attend_qtile<D, KC, F16, false, RS>(qa, Ks + head * D * 2, Vs + head * D * 2, L, lk_pad, scale_log2e, lane, o);
-        // this task is the only reader of its 16 x D patch of Qs: reuse it as the output stage
+        attend_qtile<D, KC, F16, true, 128, true>(qa, Kt, Vt, L, lk_pad, scale_log2e, lane, o, cbase);
+        // this task is the only reader of its 16 x D patch of the Q tile: reuse it as the output stage
         __syncwarp();
 #pragma unroll
         for (int dt = 0; dt < DT; ++dt) {
-            *reinterpret_cast<uint32_t*>(qh + (q0 + g) * RS + (dt * 8 + 2 * t) * 2) = pack2<F16>(o[dt][0], o[dt][1]);
-            *reinterpret_cast<uint32_t*>(qh + (q0 + g + 8) * RS + (dt * 8 + 2 * t) * 2) = pack2<F16>(o[dt][2], o[dt][3]);
+            const int r0 = q0 + g, r1 = q0 + g + 8;
+            *reinterpret_cast<uint32_t*>(Qt + r0 * 128 + (((cbase + dt) ^ (r0 & 7)) << 4) + 4 * t) = pack2<F16>(o[dt][0], o[dt][1]);
+            *reinterpret_cast<uint32_t*>(Qt + r1 * 128 + (((cbase + dt) ^ (r1 & 7)) << 4) + 4 * t) = pack2<F16>(o[dt][2], o[dt][3]);
         }
     }
     __syncthreads();
-    bf16* ob = out + static_cast<size_t>(img) * L * C + hg * (G * D);
-    for (int i = threadIdx.x; i < L * W16; i += blockDim.x) {
-        const int r = i / W16, c = i - r * W16;
-        *reinterpret_cast<uint4*>(ob + static_cast<size_t>(r) * C + c * 8) =
-            *reinterpret_cast<const uint4*>(Qs + r * RS + c * 16);
+    bf16* ob = out + static_cast<size_t>(img) * L * C + hg * 128;
+    for (int i = threadIdx.x; i < L * 16; i += blockDim.x) {
+        const int r = i >> 4, j = i & 15;
+        const uint8_t* src = sm + (j >> 3) * tile_bytes + r * 128 + (((j & 7) ^ (r & 7)) << 4);
+        *reinterpret_cast<uint4*>(ob + static_cast<size_t>(r) * C + j * 8) = *reinterpret_cast<const uint4*>(src);
     }
 }
 
@@ -275,7 +283,7 @@ attention_head_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int 
             }
         }
         float o[DT][4];
-        attend_qtile<D, KC, F16, false, RS>(qa, Ks, Vs, L, lk_pad, scale_log2e, lane, o);
+        attend_qtile<D, KC, F16, false, RS, false>(qa, Ks, Vs, L, lk_pad, scale_log2e, lane, o);
         bf16* ob = out + static_cast<size_t>(img) * L * C + head * D;
 #pragma unroll
         for (int dt = 0; dt < DT; ++dt) {

@@ -210,10 +210,13 @@ static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads
     const float scale_log2e = (1.0f / sqrtf(static_cast<float>(D))) * 1.44269504088896340736f;
     const int qtiles = (L + 15) / 16;
     constexpr int G = 128 / D;
-    const size_t gsmem = att_group_smem_bytes(L, D, KC, G);
-    if (heads % G == 0 && gsmem <= 100 * 1024) {      // >= 2 CTAs per SM: one image's head group per CTA
+    const int lk_pad = (L + KC - 1) / KC * KC;
+    const size_t gsmem = att_group_smem_bytes(L, KC);
+    if (heads % G == 0 && L <= KC && lk_pad <= 256 && gsmem <= 100 * 1024) {      // one image's head group per CTA
+        CUtensorMap tm;
+        TRY(make_tmap(&tm, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, lk_pad));
         const int warps = qtiles < ATT_GROUP_WARPS ? qtiles : ATT_GROUP_WARPS;
-        attention_group_kernel<D, KC, F16><<<dim3(heads / G, B), warps * 32, gsmem, st>>>(qkv, out, L, C, scale_log2e);
+        attention_group_kernel<D, KC, F16><<<dim3(heads / G, B), warps * 32, gsmem, st>>>(tm, out, L, C, scale_log2e);
     } else {
         const size_t smem = att_head_smem_bytes(L, D, KC);
         if (smem > 227 * 1024) return fail(DDC_E_INVALID, "attention: L=%d needs %zu B of shared memory", L, smem);
