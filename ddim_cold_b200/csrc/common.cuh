@@ -98,6 +98,13 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
         ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
+// Bring a box into L2 only (no shared memory, no barrier): used to turn a later DRAM-latency TMA load into an
+// L2 hit when the address is known long before the data is needed.
+__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* m, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];"
+                 ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1)
+                 : "memory");
+}
 // CTA-pair load: the data lands in THIS CTA's shared memory, the transaction bytes are credited to the
 // barrier at the same offset in the pair's leader CTA (even rank), which is the one that issues the MMAs.
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;      // clears the CTA-rank bit of a shared::cluster address

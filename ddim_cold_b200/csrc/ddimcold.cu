@@ -427,7 +427,7 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
     mk(&pl->tm_O, false, pl->O, Mp, C, G2_BM);
     mk(&pl->tm_Hd, false, pl->Hd, Mp, C, G2_BM);
     mk(&pl->tm_XN, false, pl->XN, Mp, C, G2_BM);
-    mk(&pl->tm_Xld, true, pl->X, Mp, C, 32);
+    mk(&pl->tm_Xld, true, pl->X, Mp, C, G2_BM);
     for (int cs = 1; cs <= 2; ++cs) {
         mk(&pl->tm_wpatch[cs - 1], false, pl->w_patch, C, pl->Kp, pl->bn_row / cs);
         mk(&pl->tm_whead[cs - 1], false, pl->w_head, pl->P, C, pl->bn_head / cs);
@@ -549,10 +549,10 @@ struct Prof {
 static int ensure_store_maps(ddc_plan* pl, int B) {
     if (pl->maps_B == B) return DDC_OK;
     const uint64_t M = static_cast<uint64_t>(B) * pl->L, C = pl->C;
-    TRY(make_tmap(&pl->st_QKV, false, pl->QKV, M, 3 * C, 32));
-    TRY(make_tmap(&pl->st_Hd, false, pl->Hd, M, C, 32));
-    TRY(make_tmap(&pl->st_XN, false, pl->XN, M, C, 32));
-    TRY(make_tmap(&pl->st_X, true, pl->X, M, C, 32));
+    TRY(make_tmap(&pl->st_QKV, false, pl->QKV, M, 3 * C, G2_BM));
+    TRY(make_tmap(&pl->st_Hd, false, pl->Hd, M, C, G2_BM));
+    TRY(make_tmap(&pl->st_XN, false, pl->XN, M, C, G2_BM));
+    TRY(make_tmap(&pl->st_X, true, pl->X, M, C, G2_BM));
     pl->maps_B = B;
     if (pl->gexec) {                 // the captured graph holds the old maps by value
         cudaGraphExecDestroy(pl->gexec);
@@ -734,7 +734,7 @@ extern "C" int ddc_forward_fixed_scratch(ddc_plan* pl, const float* x, const int
         TRY(make_tmap(&v.tm_O, false, v.O, Mp, C, G2_BM));
         TRY(make_tmap(&v.tm_Hd, false, v.Hd, Mp, C, G2_BM));
         TRY(make_tmap(&v.tm_XN, false, v.XN, Mp, C, G2_BM));
-        TRY(make_tmap(&v.tm_Xld, true, v.X, Mp, C, 32));
+        TRY(make_tmap(&v.tm_Xld, true, v.X, Mp, C, G2_BM));
         pl->fixed_view = v;
         pl->fixed_view_cap = fit;
     }
@@ -917,10 +917,10 @@ extern "C" int ddc_k_gemm(int32_t fmt, int32_t epi, int32_t M, int32_t N, int32_
     p.M = M; p.N = N; p.K = K; p.bn = bn; p.stages = pick_stages2(K, N, bn / cs, false); p.bias = bias;
     switch (epi) {
         case S_BF16:
-            TRY(make_tmap(&tmO, false, out, M, N, 32));
+            TRY(make_tmap(&tmO, false, out, M, N, G2_BM));
             return launch_gemm2<S_BF16>(tmA, tmB, tmO, tmA, tmA, p, f16, cs, st);
         case S_BF16_GELU:
-            TRY(make_tmap(&tmO, false, out, M, N, 32));
+            TRY(make_tmap(&tmO, false, out, M, N, G2_BM));
             return launch_gemm2<S_BF16_GELU>(tmA, tmB, tmO, tmA, tmA, p, f16, cs, st);
         case S_F32:
             p.out_f32 = static_cast<float*>(out); p.ld_f32 = ld_out;
@@ -942,9 +942,9 @@ extern "C" int ddc_k_gemm_resid_ln(int32_t fmt, int32_t M, int32_t C, int32_t K,
     TRY(make_tmap(&tmA, false, A, Mp, K, G2_BM));
     const int cs = gemm_cluster_size(M);
     TRY(make_tmap(&tmB, false, W, C, K, bn / cs));
-    TRY(make_tmap(&tmO, true, x, M, C, 32));
-    TRY(make_tmap(&tmR, true, x, Mp, C, 32));
-    TRY(make_tmap(&tmN, false, xn, M, C, 32));
+    TRY(make_tmap(&tmO, true, x, M, C, G2_BM));
+    TRY(make_tmap(&tmR, true, x, Mp, C, G2_BM));
+    TRY(make_tmap(&tmN, false, xn, M, C, G2_BM));
     Gemm2Params p{};
     p.M = M; p.N = C; p.K = K; p.bn = bn; p.stages = pick_stages2(K, C, bn / cs, true); p.bias = bias;
     p.ln_g = ln_g; p.ln_b = ln_b; p.ln_eps = 1e-5f;

@@ -35,11 +35,11 @@ enum { S_BF16 = 0, S_BF16_GELU = 1, S_F32 = 2, R_RESID = 3, R_EMBED = 4 };
 
 constexpr int G2_BM = 128;
 constexpr int G2_BK = 64;
-constexpr int G2_THREADS = 384;             // warp0 TMA, warp1 MMA, warp2 TMEM, warp3 spare, warps4-11 epilogue
+constexpr int G2_THREADS = 384;             // warps 0 and 3 TMA producers, warp1 MMA, warp2 TMEM, warps4-11 epilogue
 constexpr int G2_EPI_WARPS = 8;             // two warps per TMEM lane quarter, alternating column chunks
 constexpr int G2_A_KB_BYTES = G2_BM * 128;
-constexpr int G2_SLOT_BYTES = 32 * 128;     // one epilogue warp's staging unit: 32 rows x 128 B
-constexpr int G2_ES_STREAM = 1;             // staging slots per epilogue warp
+constexpr int G2_GSLOT_BYTES = 128 * 128;   // staging unit of an epilogue group (4 warps): 128 rows x 128 B
+constexpr int G2_ES_STREAM = 1;             // staging slots per epilogue group
 constexpr int G2_ES_ROW = 2;                // row-block: residual chunk in flight + chunk being processed
 constexpr int G2_TAIL_BYTES = 3072;         // barriers, TMEM slot, row-statistics exchange
 
@@ -58,6 +58,7 @@ struct Gemm2Params {
     const StepEntry* tbl;
     const int* cur;
     int B;
+    int dbg_flags;           // probes only: 1 = no X store, 2 = no residual load, 4 = no tmem_st, 8 = skip LN passes
     long long* dbg;          // optional timeline buffer (probes only): [cta < 2][role 4][64] SM clock stamps
 };
 
@@ -77,7 +78,7 @@ __host__ __device__ inline size_t gemm2_param_bytes(int N, bool rowblock) { retu
 
 inline size_t gemm2_smem_bytes(int K, int N, int bn, int stages, bool rowblock) {
     return 1024 + static_cast<size_t>(K / G2_BK) * G2_A_KB_BYTES + static_cast<size_t>(stages) * bn * 128 +
-           static_cast<size_t>(G2_EPI_WARPS) * (rowblock ? G2_ES_ROW : G2_ES_STREAM) * G2_SLOT_BYTES +
+           static_cast<size_t>(2) * (rowblock ? G2_ES_ROW : G2_ES_STREAM) * G2_GSLOT_BYTES +
            ((gemm2_param_bytes(N, rowblock) + 127) & ~static_cast<size_t>(127)) + G2_TAIL_BYTES;
 }
 
@@ -105,7 +106,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem_a + static_cast<size_t>(kblocks) * G2_A_KB_BYTES;
     uint8_t* smem_e = smem_b + static_cast<size_t>(p.stages) * b_stage_bytes;
-    float* smem_p = reinterpret_cast<float*>(smem_e + G2_EPI_WARPS * ES * G2_SLOT_BYTES);   // bias | gamma | beta
+    float* smem_p = reinterpret_cast<float*>(smem_e + 2 * ES * G2_GSLOT_BYTES);   // bias | gamma | beta
     uint64_t* bars = reinterpret_cast<uint64_t*>(
         reinterpret_cast<uint8_t*>(smem_p) + ((gemm2_param_bytes(p.N, ROWBLOCK) + 127) & ~static_cast<size_t>(127)));
     uint64_t* full_bar = bars;             // [8]  W ring: TMA -> MMA
@@ -113,9 +114,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     uint64_t* afull_bar = bars + 16;       // [8]  A K-block landed
     uint64_t* aempty_bar = bars + 24;      // [8]  A K-block no longer needed by this tile
     uint64_t* tfull_bar = bars + 32;       // [4]  accumulator stage / N tile complete
-    uint64_t* tempty_bar = bars + 36;      // [2]  accumulator drained
-    uint64_t* res_bar = bars + 38;         // [16] residual chunk landed (per epilogue warp x slot)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 54);
+    uint64_t* tempty_bar = bars + 36;      // [4]  accumulator stage drained
+    uint64_t* res_bar = bars + 40;         // [16] residual chunk landed (per epilogue group x slot)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 56);
     float* red = reinterpret_cast<float*>(bars + 64);     // [2 stats][2 halves][128 rows] partial row statistics
 
     const int warp = threadIdx.x >> 5;
@@ -126,8 +127,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const int first_tile = static_cast<int>((blockIdx.x / CS) * CS + crank);
     const int tile_step = gridDim.x;
     const bool leader = crank == 0;
+    // stream flavour: as many accumulator stages as the 512 TMEM columns hold (max 4), so the MMA issuer can run
+    // several N tiles ahead of the epilogue and the drain handshake stays off the critical path
     const uint32_t acc_stride = g2_pow2_cols(p.bn);
-    const uint32_t tmem_cols = ROWBLOCK ? g2_pow2_cols(p.N) : g2_pow2_cols(2 * acc_stride);
+    const uint32_t nacc = (512u / acc_stride) < 4u ? (512u / acc_stride) : 4u;
+    const uint32_t tmem_cols = ROWBLOCK ? g2_pow2_cols(p.N) : g2_pow2_cols(nacc * acc_stride);
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -142,8 +146,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             mbar_init(&aempty_bar[i], 1);
         }
         for (int i = 0; i < 4; ++i) mbar_init(&tfull_bar[i], 1);
-        mbar_init(&tempty_bar[0], G2_EPI_WARPS * CS);     // the leader hears from both CTAs' epilogue warps
-        mbar_init(&tempty_bar[1], G2_EPI_WARPS * CS);
+        for (int i = 0; i < 4; ++i) mbar_init(&tempty_bar[i], G2_EPI_WARPS * CS);   // both CTAs' epilogue warps
         for (int i = 0; i < 16; ++i) mbar_init(&res_bar[i], 1);
         fence_barrier_init();
     }
@@ -166,13 +169,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0) {
-        // ================================================================= TMA producer
+    if (warp == 0 || warp == 3) {
+        // ================================================================= TMA producers
+        // One thread needs several hundred cycles per TMA instruction (wait, expect_tx, issue), more than a
+        // K block's MMAs take, so two warps issue alternate loads: producer 0 the even ones, producer 1 the odd.
         if (lane == 0) {
-            uint32_t stage = 0, phase = 0, tcount = 0;
+            const uint32_t me = warp == 0 ? 0u : 1u;
+            uint32_t bit = 0, tcount = 0;          // bit: running index of W loads (stage = bit % stages)
             for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
                 const int m0 = tile * G2_BM;
-                for (int kb = 0; kb < kblocks; ++kb) {
+                for (int kb = static_cast<int>(me); kb < kblocks; kb += 2) {
                     mbar_wait(&aempty_bar[kb], (tcount & 1) ^ 1);
                     if (CS == 1) {
                         mbar_arrive_expect_tx(&afull_bar[kb], G2_A_KB_BYTES);
@@ -182,8 +188,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                         tma_load_2d_pair(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0);
                     }
                 }
+                if (me == 0 && tile + tile_step < p.num_tiles)          // next tile's A rows -> L2 while this one runs
+                    for (int kb = 0; kb < kblocks; ++kb) tma_prefetch_l2_2d(&tmA, kb * G2_BK, (tile + tile_step) * G2_BM);
                 for (int nt = 0; nt < num_nt; ++nt) {
-                    for (int kb = 0; kb < kblocks; ++kb) {
+                    for (int kb = 0; kb < kblocks; ++kb, ++bit) {
+                        if ((bit & 1u) != me) continue;
+                        const uint32_t stage = bit % static_cast<uint32_t>(p.stages);
+                        const uint32_t phase = (bit / static_cast<uint32_t>(p.stages)) & 1u;
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         if (CS == 1) {
                             mbar_arrive_expect_tx(&full_bar[stage], b_stage_bytes);
@@ -194,7 +205,6 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                             tma_load_2d_pair(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
                                              kb * G2_BK, nt * p.bn + static_cast<int>(crank) * (p.bn / CS));
                         }
-                        if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
                     }
                 }
             }
@@ -217,13 +227,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     d_tmem = tb + static_cast<uint32_t>(nt * p.bn);
                     done_bar = &tfull_bar[nt];
                 } else {
-                    const uint32_t acc = acc_it & 1;
-                    mbar_wait(&tempty_bar[acc], ((acc_it >> 1) & 1) ^ 1);
+                    const uint32_t acc = acc_it % nacc;
+                    mbar_wait(&tempty_bar[acc], ((acc_it / nacc) & 1) ^ 1);
                     d_tmem = tb + acc * acc_stride;
                     done_bar = &tfull_bar[acc];
                     ++acc_it;
                 }
                 tc_fence_after();
+                if (lane == 0) g2_stamp(p, 1, (tcount * 4 + nt) * 2);
                 for (int kb = 0; kb < kblocks; ++kb) {
                     if (nt == 0) mbar_wait(&afull_bar[kb], tcount & 1);
                     mbar_wait(&full_bar[stage], phase);
@@ -244,15 +255,21 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     __syncwarp();
                     if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
                 }
+                if (lane == 0) g2_stamp(p, 1, (tcount * 4 + nt) * 2 + 1);
             }
         }
     } else if (warp >= 4) {
         // ================================================================= epilogue
-        // warp w drains TMEM lanes [32*(w%4), +32) (thread = one output row); the two warps of a lane
-        // quarter (hf = 0/1) take alternating column chunks.
+        // warp w drains TMEM lanes [32*(w%4), +32) (thread = one output row).  The eight warps form two groups
+        // (hf = 0/1) of four that take alternating column chunks; a group shares one [128 rows x 128 B] staging
+        // slot per chunk and its leader issues ONE 16 KB TMA operation for it (a TMA instruction costs the SM's
+        // TMA unit and the issuing thread a few hundred cycles whatever its size).
         const int q = warp & 3;
         const int hf = (warp - 4) >> 2;
-        uint8_t* my_slots = smem_e + static_cast<size_t>(warp - 4) * ES * G2_SLOT_BYTES;
+        const bool gleader = q == 0 && lane == 0;
+        const int gbar = 1 + hf;                                  // named barrier of this group (128 threads)
+        uint8_t* grp_slots = smem_e + static_cast<size_t>(hf) * ES * G2_GSLOT_BYTES;
+        const int trow = q * 32 + lane;                           // this thread's row inside the 128-row tile
         const uint32_t lane_taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
         const float* s_bias = smem_p;
         uint32_t tcount = 0;
@@ -260,11 +277,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             uint32_t acc_it = 0;
             const int cpn = p.bn / 64;              // 64-column chunks per N tile (bf16 flavours)
             for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
-                const int row0 = tile * G2_BM + q * 32;
-                const int row = row0 + lane;
+                const int m0 = tile * G2_BM;
+                const int row = m0 + trow;
                 for (int nt = 0; nt < num_nt; ++nt, ++acc_it) {
-                    const uint32_t acc = acc_it & 1;
-                    mbar_wait(&tfull_bar[acc], (acc_it >> 1) & 1);
+                    const uint32_t acc = acc_it % nacc;
+                    mbar_wait(&tfull_bar[acc], (acc_it / nacc) & 1);
                     tc_fence_after();
                     const uint32_t t_row = lane_taddr + acc * acc_stride;
                     if (EPI == S_F32) {
@@ -285,9 +302,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     } else {
                         for (int c = 0; c < cpn; ++c) {
                             if (((nt * cpn + c) & 1) != hf) continue;
-                            uint8_t* slot = my_slots;
-                            if (lane == 0) bulk_wait_read<0>();      // the slot's previous store has read it
-                            __syncwarp();
+                            uint8_t* slot = grp_slots;
+                            if (gleader) bulk_wait_read<0>();      // the slot's previous store has read it
+                            named_bar_sync(gbar, 128);
                             const int n0 = nt * p.bn + c * 64;
 #pragma unroll
                             for (int h = 0; h < 2; ++h) {
@@ -309,13 +326,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                                     o.y = pack2<F16>(v[8 * j + 2], v[8 * j + 3]);
                                     o.z = pack2<F16>(v[8 * j + 4], v[8 * j + 5]);
                                     o.w = pack2<F16>(v[8 * j + 6], v[8 * j + 7]);
-                                    *reinterpret_cast<uint4*>(slot + slot_off(lane, 4 * h + j)) = o;
+                                    *reinterpret_cast<uint4*>(slot + slot_off(trow, 4 * h + j)) = o;
                                 }
                             }
                             fence_proxy_async_smem();
-                            __syncwarp();
-                            if (lane == 0 && row0 < p.M) {
-                                tma_store_2d(&tmO, slot, n0, row0);
+                            named_bar_sync(gbar, 128);
+                            if (gleader && m0 < p.M) {
+                                tma_store_2d(&tmO, slot, n0, m0);
                                 bulk_commit();
                             }
                         }
@@ -327,20 +344,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             }
         } else {
             // ---------------------------------------------------------- row-block flavour
-            const int nchunk = p.N / 32;            // fp32 chunks of 128 B per row; this warp takes c % 2 == hf
+            const int nchunk = p.N / 32;            // fp32 chunks of 128 B per row; this group takes c % 2 == hf
             const float inv_n = 1.0f / static_cast<float>(p.N);
             const float* s_gamma = smem_p + p.N;
             const float* s_beta = smem_p + 2 * p.N;
-            float* red_sum = red + hf * 128 + q * 32 + lane;
-            float* red_sq = red + 256 + hf * 128 + q * 32 + lane;
-            const float* oth_sum = red + (hf ^ 1) * 128 + q * 32 + lane;
-            const float* oth_sq = red + 256 + (hf ^ 1) * 128 + q * 32 + lane;
-            uint64_t* my_res = res_bar + (warp - 4) * ES;
-            uint32_t ri = 0;                        // staging-slot counter (this warp)
+            float* red_sum = red + hf * 128 + trow;
+            float* red_sq = red + 256 + hf * 128 + trow;
+            const float* oth_sum = red + (hf ^ 1) * 128 + trow;
+            const float* oth_sq = red + 256 + (hf ^ 1) * 128 + trow;
+            uint64_t* my_res = res_bar + hf * ES;
+            uint32_t ri = 0;                        // staging-slot counter (this group)
             uint32_t res_phase = 0;                 // per-slot parity of the residual barriers (bit s)
+            // The residual X rows come from DRAM; with one chunk of look-ahead per group every chunk would pay a
+            // full DRAM latency.  Their addresses are known a whole tile early, so the group leader pulls the NEXT
+            // tile's chunks into L2 while this tile is processed (and this tile's right away for the first one).
+            if (EPI == R_RESID && gleader && first_tile < p.num_tiles)
+                for (int c = hf; c < nchunk; c += 2) tma_prefetch_l2_2d(&tmR, c * 32, first_tile * G2_BM);
             for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
-                const int row0 = tile * G2_BM + q * 32;
-                const int row = row0 + lane;
+                const int m0 = tile * G2_BM;
+                const int row = m0 + trow;
+                if (EPI == R_RESID && gleader && tile + tile_step < p.num_tiles)
+                    for (int c = hf; c < nchunk; c += 2) tma_prefetch_l2_2d(&tmR, c * 32, (tile + tile_step) * G2_BM);
                 const float* embed_pos = nullptr;
                 const float* embed_time = nullptr;
                 if (EPI == R_EMBED) {
@@ -351,29 +375,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     embed_pos = p.posb + static_cast<size_t>(l) * p.N;
                     embed_time = p.time_tab + static_cast<size_t>(t) * p.N;
                 }
-                if (EPI == R_RESID && hf < nchunk) {
-                    if (lane == 0) {
-                        bulk_wait_read<0>();        // slots may still feed the previous tile's XN stores
-                        const uint32_t s = ri % ES;
-                        mbar_arrive_expect_tx(&my_res[s], G2_SLOT_BYTES);
-                        tma_load_2d(my_slots + s * G2_SLOT_BYTES, &tmR, &my_res[s], hf * 32, row0);
-                    }
-                    __syncwarp();
+                if (EPI == R_RESID && hf < nchunk && gleader && !(p.dbg_flags & 2)) {
+                    bulk_wait_read<0>();            // slots may still feed the previous tile's XN stores
+                    const uint32_t s = ri % ES;
+                    mbar_arrive_expect_tx(&my_res[s], G2_GSLOT_BYTES);
+                    tma_load_2d(grp_slots + s * G2_GSLOT_BYTES, &tmR, &my_res[s], hf * 32, m0);
                 }
+                if (warp == 4 && lane == 0) g2_stamp(p, 2, tcount * 4);
                 float sum = 0.f;
                 int waited_nt = -1;
                 for (int c = hf; c < nchunk; c += 2, ++ri) {
                     const uint32_t s = ri % ES;
-                    uint8_t* slot = my_slots + s * G2_SLOT_BYTES;
-                    if (lane == 0) {
+                    uint8_t* slot = grp_slots + s * G2_GSLOT_BYTES;
+                    if (gleader) {
                         bulk_wait_read<0>();        // the other slot's store (previous chunk) has released it
-                        if (EPI == R_RESID && c + 2 < nchunk) {
+                        if (EPI == R_RESID && c + 2 < nchunk && !(p.dbg_flags & 2)) {
                             const uint32_t s2 = (ri + 1) % ES;
-                            mbar_arrive_expect_tx(&my_res[s2], G2_SLOT_BYTES);
-                            tma_load_2d(my_slots + s2 * G2_SLOT_BYTES, &tmR, &my_res[s2], (c + 2) * 32, row0);
+                            mbar_arrive_expect_tx(&my_res[s2], G2_GSLOT_BYTES);
+                            tma_load_2d(grp_slots + s2 * G2_GSLOT_BYTES, &tmR, &my_res[s2], (c + 2) * 32, m0);
                         }
                     }
-                    __syncwarp();
+                    if (EPI == R_EMBED) named_bar_sync(gbar, 128);     // slot free for every warp of the group
                     const int n0 = c * 32;
                     const int nt = n0 / p.bn;
                     if (nt != waited_nt) {
@@ -384,11 +406,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     float v[32];
                     tmem_ld32(lane_taddr + n0, v);
                     if (EPI == R_RESID) {
-                        mbar_wait(&my_res[s], (res_phase >> s) & 1);
-                        res_phase ^= (1u << s);
+                        if (!(p.dbg_flags & 2)) {
+                            mbar_wait(&my_res[s], (res_phase >> s) & 1);
+                            res_phase ^= (1u << s);
+                        }
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
-                            const float4 r = *reinterpret_cast<const float4*>(slot + slot_off(lane, j));
+                            const float4 r = *reinterpret_cast<const float4*>(slot + slot_off(trow, j));
                             const float4 b = *reinterpret_cast<const float4*>(s_bias + n0 + 4 * j);
                             v[4 * j] += r.x + b.x; v[4 * j + 1] += r.y + b.y;
                             v[4 * j + 2] += r.z + b.z; v[4 * j + 3] += r.w + b.w;
@@ -404,22 +428,23 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     }
 #pragma unroll
                     for (int i = 0; i < 32; ++i) sum += v[i];
-                    tmem_st32(lane_taddr + n0, v);
+                    if (!(p.dbg_flags & 4)) tmem_st32(lane_taddr + n0, v);
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
-                        *reinterpret_cast<float4*>(slot + slot_off(lane, j)) =
+                        *reinterpret_cast<float4*>(slot + slot_off(trow, j)) =
                             make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                     fence_proxy_async_smem();
-                    __syncwarp();
-                    if (lane == 0 && row0 < p.M) {
-                        tma_store_2d(&tmO, slot, n0, row0);
+                    named_bar_sync(gbar, 128);
+                    if (gleader && m0 < p.M && !(p.dbg_flags & 1)) {
+                        tma_store_2d(&tmO, slot, n0, m0);
                         bulk_commit();
                     }
                 }
                 // ---- row statistics: exact two-pass variance; the two column halves exchange partials
+                if (warp == 4 && lane == 0) g2_stamp(p, 2, tcount * 4 + 1);
                 *red_sum = sum;
                 tc_fence_before();                  // the partner's pass 3 reads TMEM columns this warp stored
-                named_bar_sync(1 + q, 64);
+                named_bar_sync(3 + q, 64);
                 tc_fence_after();
                 const float mean = (sum + *oth_sum) * inv_n;
                 float sq = 0.f;
@@ -433,12 +458,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     }
                 }
                 *red_sq = sq;
-                named_bar_sync(1 + q, 64);
+                named_bar_sync(3 + q, 64);
                 const float rstd = rsqrtf((sq + *oth_sq) * inv_n + p.ln_eps);
-                for (int c = hf; c < p.N / 64; c += 2, ++ri) {
-                    uint8_t* slot = my_slots + (ri % ES) * G2_SLOT_BYTES;
-                    if (lane == 0) bulk_wait_read<ES - 1>();
-                    __syncwarp();
+                if (warp == 4 && lane == 0) g2_stamp(p, 2, tcount * 4 + 2);
+                for (int c = hf; c < ((p.dbg_flags & 8) ? 0 : p.N / 64); c += 2, ++ri) {
+                    uint8_t* slot = grp_slots + (ri % ES) * G2_GSLOT_BYTES;
+                    if (gleader) bulk_wait_read<ES - 1>();
+                    named_bar_sync(gbar, 128);
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
                         float v[32];
@@ -455,22 +481,23 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                             o.y = pack2<F16>((v[8 * j + 2] - mean) * rstd * g0.z + b0.z, (v[8 * j + 3] - mean) * rstd * g0.w + b0.w);
                             o.z = pack2<F16>((v[8 * j + 4] - mean) * rstd * g1.x + b1.x, (v[8 * j + 5] - mean) * rstd * g1.y + b1.y);
                             o.w = pack2<F16>((v[8 * j + 6] - mean) * rstd * g1.z + b1.z, (v[8 * j + 7] - mean) * rstd * g1.w + b1.w);
-                            *reinterpret_cast<uint4*>(slot + slot_off(lane, 4 * h + j)) = o;
+                            *reinterpret_cast<uint4*>(slot + slot_off(trow, 4 * h + j)) = o;
                         }
                     }
                     fence_proxy_async_smem();
-                    __syncwarp();
-                    if (lane == 0 && row0 < p.M) {
-                        tma_store_2d(&tmN, slot, c * 64, row0);
+                    named_bar_sync(gbar, 128);
+                    if (gleader && m0 < p.M) {
+                        tma_store_2d(&tmN, slot, c * 64, m0);
                         bulk_commit();
                     }
                 }
                 tc_fence_before();
                 __syncwarp();
+                if (warp == 4 && lane == 0) g2_stamp(p, 2, tcount * 4 + 3);
                 if (lane == 0) { if (CS == 1) mbar_arrive(&tempty_bar[0]); else mbar_arrive_leader(&tempty_bar[0]); }
             }
         }
-        if (lane == 0) bulk_wait_all();      // smem must outlive the last TMA stores
+        if (gleader) bulk_wait_all();        // smem must outlive the last TMA stores
         __syncwarp();
     }
 
