@@ -48,8 +48,8 @@ __device__ __forceinline__ uint32_t att_addr(const uint8_t* base, int row, int c
     return SWZ ? smem_u32(base + row * 128 + ((chunk ^ (row & 7)) << 4)) : smem_u32(base + row * RS + (chunk << 4));
 }
 
-// SINGLE: the whole key range is one chunk (L <= KC; att_pick_kc then guarantees L > KC - 16), so only the last
-// two n-tiles can reach past L and the mask is resolved at compile time for all the others.
+// SINGLE: the whole key range is one chunk and KC - 16 < L <= KC, so only the last two n-tiles can reach past L
+// and the mask is resolved at compile time for all the others (the caller checks the condition).
 template <int D, int KC, bool F16, bool SWZ, int PITCH, bool SINGLE>
 __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], const uint8_t* Ks, const uint8_t* Vs,
                                              int L, int lk_pad, float scale_log2e, int lane,
@@ -210,7 +210,8 @@ attention_group_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restri
             ldmatrix_x4(qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], att_addr<true>(Qt, qrow, cbase + ks * 2 + (lane >> 4), 0));
         }
         float o[DT][4];
-        attend_qtile<D, KC, F16, true, 128, true>(qa, Kt, Vt, L, lk_pad, scale_log2e, lane, o, cbase);
+        if (L > KC - 16) attend_qtile<D, KC, F16, true, 128, true>(qa, Kt, Vt, L, lk_pad, scale_log2e, lane, o, cbase);
+        else attend_qtile<D, KC, F16, true, 128, false>(qa, Kt, Vt, L, lk_pad, scale_log2e, lane, o, cbase);
         // this task is the only reader of its 16 x D patch of the Q tile: reuse it as the output stage
         __syncwarp();
 #pragma unroll

@@ -1,0 +1,485 @@
+// Fused tail of a transformer block (ViT.py:136-137 with Mlp.forward :84-90 and the next LayerNorm):
+//
+//     X1 = X + O * Wproj^T + b_proj                       (attention projection + residual)
+//     H  = gelu_erf(LayerNorm2(X1) * Wfc1^T + b_fc1)
+//     X' = X1 + H * Wfc2^T + b_fc2                        (MLP + residual)        -> X  (fp32)
+//     XN = LayerNorm_next(X')                                                      -> XN (16 bit)
+//
+// in ONE persistent kernel: three GEMMs share a tile's fixed costs, X is read and written once per block, and
+// the 16-bit intermediates (LayerNorm2 output, H) never leave the SM.  Per 128-row tile of a CTA pair
+// (cta_group::2, M = 256), with C = embed_dim (multiple of 128, <= 384), NB = C/128, KB = C/64:
+//
+//   TMEM   cols [0, C)      the fp32 row block: proj accumulator -> X1 -> fc2 accumulates on top of it
+//          cols [C, C+128)  fc1 accumulator for one 128-wide hidden block
+//   smem   Abuf  KB x 16 KB  O tile (TMA), later overwritten by LayerNorm2(X1) in the same swizzled K-major layout
+//          Hbuf  2 x 32 KB   one hidden block of H each (two K blocks); doubles as staging for residual loads
+//                            (phase 1) and for the X / XN stores (phase 3) while no hidden block is live
+//          W ring            64-row halves of 128 x 64 weight tiles, streamed in MMA order
+//
+//   MMA order   proj(n = 0..NB-1) | for j: fc1(j) ; fc2 partial(j): X1[:, n-tile] += H_j * Wfc2[n-tile, j-th K range]
+//   epilogue    epi1: + residual + bias -> TMEM, exact two-pass LayerNorm2 -> Abuf
+//               epi2(j): + bias, GELU -> Hbuf[j & 1]
+//               epi3: + bias -> X (TMA store), exact two-pass LayerNorm_next -> XN (TMA store)
+#pragma once
+
+#include "common.cuh"
+#include "gemm2.cuh"
+
+namespace ddc {
+
+constexpr int BT_THREADS = 384;              // warps 0,3 TMA, warp1 MMA (pair leader), warp2 TMEM, warps 4-11 epilogue
+constexpr int BT_BN = 128;                   // N tile of every GEMM in here
+constexpr int BT_HSLOT_BYTES = 2 * G2_A_KB_BYTES;   // one hidden block: 128 rows x 128 cols, two K blocks
+
+struct BlockTailParams {
+    int M, C, stages, num_tiles;
+    const float* b_proj;
+    const float* ln2_g;
+    const float* ln2_b;
+    const float* b_fc1;
+    const float* b_fc2;
+    const float* lnn_g;      // LayerNorm that follows the block (next block's norm1, or the final norm)
+    const float* lnn_b;
+    float ln_eps;
+    long long* dbg;          // probes only: [role 2][64] SM clock stamps of CTA 0
+};
+
+__device__ __forceinline__ void bt_stamp(const BlockTailParams& p, int role, int idx) {
+    if (p.dbg != nullptr && blockIdx.x == 0 && idx < 64) p.dbg[role * 64 + idx] = clock64();
+}
+
+inline size_t block_tail_smem_bytes(int C, int stages) {
+    return 1024 + static_cast<size_t>(C / 64) * G2_A_KB_BYTES + 2 * BT_HSLOT_BYTES + static_cast<size_t>(stages) * 64 * 128 +
+           ((static_cast<size_t>(7) * C * 4 + 127) & ~static_cast<size_t>(127)) + G2_TAIL_BYTES;
+}
+
+template <bool F16>
+__global__ void __launch_bounds__(BT_THREADS, 1)
+block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad, C] 16 bit, box 64 x 128 (A operand)
+                  const __grid_constant__ CUtensorMap tmWp,     // Wproj  [C, C]    16 bit, box 64 x 64
+                  const __grid_constant__ CUtensorMap tmW1,     // Wfc1
+                  const __grid_constant__ CUtensorMap tmW2,     // Wfc2
+                  const __grid_constant__ CUtensorMap tmXld,    // X      [Mpad, C] fp32,  box 32 x 128 (residual)
+                  const __grid_constant__ CUtensorMap tmXst,    // X      [M, C]    fp32,  box 32 x 128 (store)
+                  const __grid_constant__ CUtensorMap tmXN,     // XN     [M, C]    16 bit, box 64 x 128 (store)
+                  const BlockTailParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw_addr = smem_u32(smem_raw);
+    uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+    const int C = p.C;
+    const int KB = C / 64;                       // K blocks of every GEMM (K == C)
+    const int NB = C / BT_BN;                    // N tiles == hidden blocks
+    constexpr uint32_t kStageBytes = 64 * 128;   // this CTA's half (64 rows) of a 128 x 64 weight tile
+    uint8_t* abuf = smem;
+    uint8_t* hbuf = abuf + static_cast<size_t>(KB) * G2_A_KB_BYTES;
+    uint8_t* ring = hbuf + 2 * BT_HSLOT_BYTES;
+    float* sp = reinterpret_cast<float*>(ring + static_cast<size_t>(p.stages) * kStageBytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sp) +
+                                                 ((static_cast<size_t>(7) * C * 4 + 127) & ~static_cast<size_t>(127)));
+    uint64_t* full_bar = bars;            // [8]  W ring: TMA -> MMA            (leader's copy collects both CTAs' bytes)
+    uint64_t* empty_bar = bars + 8;       // [8]  W ring: MMA -> TMA            (pair commit)
+    uint64_t* afull_bar = bars + 16;      // [8]  O K block landed              (leader)
+    uint64_t* aempty_bar = bars + 24;     // [1]  Abuf no longer read by fc1    (pair commit)
+    uint64_t* proj_bar = bars + 25;       // [4]  proj N tile complete          (pair commit)
+    uint64_t* ln2_bar = bars + 29;        // [1]  LayerNorm2 output in Abuf     (leader, 8 warps x 2 CTAs)
+    uint64_t* t1full_bar = bars + 30;     // [1]  fc1 accumulator complete      (pair commit)
+    uint64_t* t1free_bar = bars + 31;     // [1]  fc1 accumulator drained       (leader, 16 arrivals)
+    uint64_t* hready_bar = bars + 32;     // [2]  hidden block written          (leader, 16 arrivals)
+    uint64_t* hfree_bar = bars + 34;      // [2]  hidden block consumed by fc2  (pair commit)
+    uint64_t* final_bar = bars + 36;      // [1]  row block holds X1 + H Wfc2^T (pair commit)
+    uint64_t* tfree_bar = bars + 37;      // [1]  row block drained by epi3     (leader, 16 arrivals)
+    uint64_t* res_bar = bars + 38;        // [4]  residual chunk landed (group x slot)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 48);
+    float* red = reinterpret_cast<float*>(bars + 64);     // [2 stats][2 groups][128 rows]
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t crank = cluster_ctarank();
+    const bool leader = crank == 0;
+    const int first_tile = static_cast<int>(blockIdx.x);       // the pair takes tiles (2c, 2c+1), (2c + grid, ...), ...
+    const int tile_step = gridDim.x;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmO); tma_prefetch_desc(&tmWp); tma_prefetch_desc(&tmW1); tma_prefetch_desc(&tmW2);
+        tma_prefetch_desc(&tmXld); tma_prefetch_desc(&tmXst); tma_prefetch_desc(&tmXN);
+        for (int i = 0; i < 8; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+            mbar_init(&afull_bar[i], 1);
+        }
+        mbar_init(aempty_bar, 1);
+        for (int i = 0; i < 4; ++i) mbar_init(&proj_bar[i], 1);
+        mbar_init(ln2_bar, 16);
+        mbar_init(t1full_bar, 1);
+        mbar_init(t1free_bar, 16);
+        mbar_init(&hready_bar[0], 16);
+        mbar_init(&hready_bar[1], 16);
+        mbar_init(&hfree_bar[0], 1);
+        mbar_init(&hfree_bar[1], 1);
+        mbar_init(final_bar, 1);
+        mbar_init(tfree_bar, 16);
+        for (int i = 0; i < 4; ++i) mbar_init(&res_bar[i], 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) {
+        tmem_alloc<2>(tmem_slot, 512);
+        tmem_relinquish<2>();
+    }
+    if (warp >= 4) {
+        const float* src[7] = {p.b_proj, p.ln2_g, p.ln2_b, p.b_fc1, p.b_fc2, p.lnn_g, p.lnn_b};
+        for (int i = threadIdx.x - 128; i < 7 * C; i += 256) sp[i] = src[i / C][i % C];
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const float* s_bproj = sp;
+    const float* s_g2 = sp + C;
+    const float* s_b2 = sp + 2 * C;
+    const float* s_bfc1 = sp + 3 * C;
+    const float* s_bfc2 = sp + 4 * C;
+    const float* s_gn = sp + 5 * C;
+    const float* s_bn = sp + 6 * C;
+
+    if (warp == 0 || warp == 3) {
+        // ================================================================= TMA producers (alternate loads)
+        if (lane == 0) {
+            const uint32_t me = warp == 0 ? 0u : 1u;
+            uint32_t bit = 0, tc = 0;
+            auto load_w = [&](const CUtensorMap* tm, int kcol, int row0) {
+                if ((bit & 1u) == me) {
+                    const uint32_t stage = bit % static_cast<uint32_t>(p.stages);
+                    const uint32_t phase = (bit / static_cast<uint32_t>(p.stages)) & 1u;
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * kStageBytes);
+                    tma_load_2d_pair(ring + static_cast<size_t>(stage) * kStageBytes, tm, &full_bar[stage], kcol,
+                                     row0 + static_cast<int>(crank) * 64);
+                }
+                ++bit;
+            };
+            for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tc) {
+                const int m0 = tile * G2_BM;
+                mbar_wait(aempty_bar, (tc & 1) ^ 1);                 // fc1 of the previous tile has read Abuf
+                for (int kb = static_cast<int>(me); kb < KB; kb += 2) {
+                    if (leader) mbar_arrive_expect_tx(&afull_bar[kb], 2 * G2_A_KB_BYTES);
+                    tma_load_2d_pair(abuf + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmO, &afull_bar[kb], kb * 64, m0);
+                }
+                if (me == 0 && tile + tile_step < p.num_tiles)       // next tile's O rows -> L2
+                    for (int kb = 0; kb < KB; ++kb) tma_prefetch_l2_2d(&tmO, kb * 64, (tile + tile_step) * G2_BM);
+                for (int n = 0; n < NB; ++n)
+                    for (int kb = 0; kb < KB; ++kb) load_w(&tmWp, kb * 64, n * BT_BN);
+                for (int j = 0; j < NB; ++j) {
+                    for (int kb = 0; kb < KB; ++kb) load_w(&tmW1, kb * 64, j * BT_BN);
+                    for (int n = 0; n < NB; ++n)
+                        for (int kk = 0; kk < 2; ++kk) load_w(&tmW2, (2 * j + kk) * 64, n * BT_BN);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1 && leader) {
+        // ================================================================= MMA issuer (pair leader)
+        const uint32_t idesc = umma_idesc_16bit(256, BT_BN, F16);
+        const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+        const uint64_t ad0 = umma_desc_sw128(smem_u32(abuf));
+        const uint64_t hd0 = umma_desc_sw128(smem_u32(hbuf));
+        const uint64_t bd0 = umma_desc_sw128(smem_u32(ring));
+        constexpr uint32_t kStageUnits = kStageBytes >> 4;
+        constexpr uint32_t kKbUnits = G2_A_KB_BYTES >> 4;
+        uint32_t bit = 0, tc = 0, g = 0;          // g: running hidden-block index (H slot = g & 1)
+        auto mma_step = [&](uint32_t d_tmem, uint64_t adesc, uint32_t accumulate) {
+            const uint32_t stage = bit % static_cast<uint32_t>(p.stages);
+            const uint32_t phase = (bit / static_cast<uint32_t>(p.stages)) & 1u;
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            if (elect_one()) {
+                umma_kblock<2>(d_tmem, adesc, bd0 + static_cast<uint64_t>(stage * kStageUnits), idesc, accumulate);
+                umma_commit_pair(&empty_bar[stage]);
+            }
+            __syncwarp();
+            ++bit;
+        };
+        for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tc) {
+            mbar_wait(tfree_bar, (tc & 1) ^ 1);                      // epi3 of the previous tile has drained TMEM
+            tc_fence_after();
+            if (lane == 0) bt_stamp(p, 0, tc * 16 + 0);
+            // ---- proj: row block <- O * Wproj^T
+            for (int n = 0; n < NB; ++n) {
+                for (int kb = 0; kb < KB; ++kb) {
+                    if (n == 0) { mbar_wait(&afull_bar[kb], tc & 1); tc_fence_after(); }
+                    mma_step(tb + static_cast<uint32_t>(n * BT_BN), ad0 + static_cast<uint64_t>(kb * kKbUnits), kb != 0);
+                }
+                if (elect_one()) umma_commit_pair(&proj_bar[n]);
+                __syncwarp();
+            }
+            if (lane == 0) bt_stamp(p, 0, tc * 16 + 1);
+            // ---- MLP: Abuf now receives LayerNorm2(X1) from the epilogue warps of both CTAs
+            mbar_wait(ln2_bar, tc & 1);
+            tc_fence_after();
+            if (lane == 0) bt_stamp(p, 0, tc * 16 + 2);
+            for (int j = 0; j < NB; ++j, ++g) {
+                const uint32_t hs = g & 1u;
+                mbar_wait(t1free_bar, (g & 1u) ^ 1u);                 // fc1 accumulator drained by epi2(g - 1)
+                tc_fence_after();
+                for (int kb = 0; kb < KB; ++kb)
+                    mma_step(tb + static_cast<uint32_t>(C), ad0 + static_cast<uint64_t>(kb * kKbUnits), kb != 0);
+                if (lane == 0) bt_stamp(p, 0, tc * 16 + 3 + 4 * j);
+                if (elect_one()) {
+                    umma_commit_pair(t1full_bar);
+                    if (j == NB - 1) umma_commit_pair(aempty_bar);  // Abuf may take the next tile's O
+                }
+                __syncwarp();
+                mbar_wait(&hready_bar[hs], (g >> 1) & 1u);            // epi2 wrote hidden block g into Hbuf[hs]
+                tc_fence_after();
+                if (lane == 0) bt_stamp(p, 0, tc * 16 + 4 + 4 * j);
+                for (int n = 0; n < NB; ++n)
+                    for (int kk = 0; kk < 2; ++kk)
+                        mma_step(tb + static_cast<uint32_t>(n * BT_BN),
+                                 hd0 + static_cast<uint64_t>(hs * (BT_HSLOT_BYTES >> 4) + kk * kKbUnits), 1u);
+                if (lane == 0) bt_stamp(p, 0, tc * 16 + 5 + 4 * j);
+                if (elect_one()) {
+                    umma_commit_pair(&hfree_bar[hs]);
+                    if (j == NB - 1) umma_commit_pair(final_bar);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp >= 4) {
+        // ================================================================= epilogue (8 warps, two groups of four)
+        const int q = warp & 3;
+        const int hf = (warp - 4) >> 2;
+        const bool gleader = q == 0 && lane == 0;
+        const int gbar = 1 + hf;
+        const int trow = q * 32 + lane;
+        const uint32_t lane_taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+        uint8_t* gslots = hbuf + static_cast<size_t>(hf) * BT_HSLOT_BYTES;     // two 16 KB staging slots per group
+        uint64_t* my_res = res_bar + hf * 2;
+        const int nchunk = C / 32;
+        const float inv_c = 1.0f / static_cast<float>(C);
+        float* red_sum = red + hf * 128 + trow;
+        float* red_sq = red + 256 + hf * 128 + trow;
+        const float* oth_sum = red + (hf ^ 1) * 128 + trow;
+        const float* oth_sq = red + 256 + (hf ^ 1) * 128 + trow;
+        uint32_t tc = 0, g = 0, ri = 0, res_phase = 0;
+
+        // exact two-pass LayerNorm statistics of the row held in TMEM (+ `add`), shared between the two groups
+        auto row_stats = [&](float sum, const float* add, float& mean, float& rstd) {
+            *red_sum = sum;
+            tc_fence_before();
+            named_bar_sync(3 + q, 64);
+            tc_fence_after();
+            mean = (sum + *oth_sum) * inv_c;
+            float sq = 0.f;
+            for (int c = hf; c < nchunk; c += 2) {
+                float v[32];
+                tmem_ld32(lane_taddr + c * 32, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float d = v[i] + (add ? add[c * 32 + i] : 0.f) - mean;
+                    sq += d * d;
+                }
+            }
+            *red_sq = sq;
+            named_bar_sync(3 + q, 64);
+            rstd = rsqrtf((sq + *oth_sq) * inv_c + p.ln_eps);
+        };
+
+        if (gleader && first_tile < p.num_tiles)
+            for (int c = hf; c < nchunk; c += 2) tma_prefetch_l2_2d(&tmXld, c * 32, first_tile * G2_BM);
+        for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tc) {
+            const int m0 = tile * G2_BM;
+            if (gleader && tile + tile_step < p.num_tiles)
+                for (int c = hf; c < nchunk; c += 2) tma_prefetch_l2_2d(&tmXld, c * 32, (tile + tile_step) * G2_BM);
+
+            // ------------------------------------------------------------ epi1: X1 = acc + b_proj + X -> TMEM
+            if (gleader) {
+                bulk_wait_read<0>();               // the previous tile's X / XN stores have read the staging slots
+                const uint32_t s = ri & 1u;
+                mbar_arrive_expect_tx(&my_res[s], G2_GSLOT_BYTES);
+                tma_load_2d(gslots + s * G2_GSLOT_BYTES, &tmXld, &my_res[s], hf * 32, m0);
+            }
+            if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 0);
+            float sum = 0.f;
+            int waited = -1;
+            for (int c = hf; c < nchunk; c += 2, ++ri) {
+                const uint32_t s = ri & 1u;
+                uint8_t* slot = gslots + s * G2_GSLOT_BYTES;
+                if (gleader && c + 2 < nchunk) {   // the other slot was fully consumed one iteration ago (no stores here)
+                    const uint32_t s2 = s ^ 1u;
+                    mbar_arrive_expect_tx(&my_res[s2], G2_GSLOT_BYTES);
+                    tma_load_2d(gslots + s2 * G2_GSLOT_BYTES, &tmXld, &my_res[s2], (c + 2) * 32, m0);
+                }
+                const int n0 = c * 32;
+                if (n0 / BT_BN != waited) {
+                    waited = n0 / BT_BN;
+                    mbar_wait(&proj_bar[waited], tc & 1);
+                    tc_fence_after();
+                }
+                float v[32];
+                tmem_ld32(lane_taddr + n0, v);
+                mbar_wait(&my_res[s], (res_phase >> s) & 1);
+                res_phase ^= (1u << s);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float4 r = *reinterpret_cast<const float4*>(slot + slot_off(trow, j));
+                    const float4 b = *reinterpret_cast<const float4*>(s_bproj + n0 + 4 * j);
+                    v[4 * j] += r.x + b.x; v[4 * j + 1] += r.y + b.y;
+                    v[4 * j + 2] += r.z + b.z; v[4 * j + 3] += r.w + b.w;
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) sum += v[i];
+                tmem_st32(lane_taddr + n0, v);
+                named_bar_sync(gbar, 128);         // every warp of the group has read the slot before it is refilled
+            }
+            if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 1);
+            float mean, rstd;
+            row_stats(sum, nullptr, mean, rstd);
+            // LayerNorm2 -> Abuf (K-major, 128-byte swizzle: 64 columns = one K block).  All proj MMAs that read
+            // the O tile in Abuf completed before proj_bar[NB-1] fired.
+            for (int c = hf; c < C / 64; c += 2) {
+                uint8_t* kblk = abuf + static_cast<size_t>(c) * G2_A_KB_BYTES;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float v[32];
+                    const int n0 = c * 64 + 32 * h;
+                    tmem_ld32(lane_taddr + n0, v);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float4 g0 = *reinterpret_cast<const float4*>(s_g2 + n0 + 8 * j);
+                        const float4 g1 = *reinterpret_cast<const float4*>(s_g2 + n0 + 8 * j + 4);
+                        const float4 b0 = *reinterpret_cast<const float4*>(s_b2 + n0 + 8 * j);
+                        const float4 b1 = *reinterpret_cast<const float4*>(s_b2 + n0 + 8 * j + 4);
+                        uint4 o;
+                        o.x = pack2<F16>((v[8 * j] - mean) * rstd * g0.x + b0.x, (v[8 * j + 1] - mean) * rstd * g0.y + b0.y);
+                        o.y = pack2<F16>((v[8 * j + 2] - mean) * rstd * g0.z + b0.z, (v[8 * j + 3] - mean) * rstd * g0.w + b0.w);
+                        o.z = pack2<F16>((v[8 * j + 4] - mean) * rstd * g1.x + b1.x, (v[8 * j + 5] - mean) * rstd * g1.y + b1.y);
+                        o.w = pack2<F16>((v[8 * j + 6] - mean) * rstd * g1.z + b1.z, (v[8 * j + 7] - mean) * rstd * g1.w + b1.w);
+                        *reinterpret_cast<uint4*>(kblk + slot_off(trow, 4 * h + j)) = o;
+                    }
+                }
+            }
+            fence_proxy_async_smem();              // generic writes -> visible to the tensor core's operand reads
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(ln2_bar);
+            if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 2);
+
+            // ------------------------------------------------------------ epi2(j): H_j = gelu(acc + b_fc1) -> Hbuf
+            for (int j = 0; j < NB; ++j, ++g) {
+                const uint32_t hs = g & 1u;
+                mbar_wait(t1full_bar, g & 1u);
+                tc_fence_after();
+                if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 3 + 2 * j);
+                if (g >= 2) mbar_wait(&hfree_bar[hs], ((g >> 1) & 1u) ^ 1u);   // fc2 partial(g-2) has read this slot
+                // group hf converts hidden columns [64*hf, +64) of the block = K block hf of the slot
+                uint8_t* kblk = hbuf + static_cast<size_t>(hs) * BT_HSLOT_BYTES + static_cast<size_t>(hf) * G2_A_KB_BYTES;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float v[32];
+                    const int c0 = hf * 64 + 32 * h;
+                    tmem_ld32(lane_taddr + static_cast<uint32_t>(C) + c0, v);
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4) {
+                        const float4 b = *reinterpret_cast<const float4*>(s_bfc1 + j * BT_BN + c0 + i);
+                        v[i] = gelu_erf(v[i] + b.x); v[i + 1] = gelu_erf(v[i + 1] + b.y);
+                        v[i + 2] = gelu_erf(v[i + 2] + b.z); v[i + 3] = gelu_erf(v[i + 3] + b.w);
+                    }
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) {
+                        uint4 o;
+                        o.x = pack2<F16>(v[8 * jj], v[8 * jj + 1]);
+                        o.y = pack2<F16>(v[8 * jj + 2], v[8 * jj + 3]);
+                        o.z = pack2<F16>(v[8 * jj + 4], v[8 * jj + 5]);
+                        o.w = pack2<F16>(v[8 * jj + 6], v[8 * jj + 7]);
+                        *reinterpret_cast<uint4*>(kblk + slot_off(trow, 4 * h + jj)) = o;
+                    }
+                }
+                fence_proxy_async_smem();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive_leader(&hready_bar[hs]);
+                    mbar_arrive_leader(t1free_bar);
+                }
+                if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 4 + 2 * j);
+            }
+
+            // ------------------------------------------------------------ epi3: X' = TMEM + b_fc2 -> X, LN_next -> XN
+            mbar_wait(final_bar, tc & 1);
+            tc_fence_after();
+            if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 9);
+            sum = 0.f;
+            for (int c = hf; c < nchunk; c += 2, ++ri) {
+                uint8_t* slot = gslots + (ri & 1u) * G2_GSLOT_BYTES;
+                if (gleader) bulk_wait_read<1>();
+                named_bar_sync(gbar, 128);
+                const int n0 = c * 32;
+                float v[32];
+                tmem_ld32(lane_taddr + n0, v);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float4 b = *reinterpret_cast<const float4*>(s_bfc2 + n0 + 4 * j);
+                    v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+                    *reinterpret_cast<float4*>(slot + slot_off(trow, j)) =
+                        make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                }
+#pragma unroll
+                for (int i = 0; i < 32; ++i) sum += v[i];
+                fence_proxy_async_smem();
+                named_bar_sync(gbar, 128);
+                if (gleader && m0 < p.M) {
+                    tma_store_2d(&tmXst, slot, n0, m0);
+                    bulk_commit();
+                }
+            }
+            if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 10);
+            row_stats(sum, s_bfc2, mean, rstd);
+            for (int c = hf; c < C / 64; c += 2, ++ri) {
+                uint8_t* slot = gslots + (ri & 1u) * G2_GSLOT_BYTES;
+                if (gleader) bulk_wait_read<1>();
+                named_bar_sync(gbar, 128);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float v[32];
+                    const int n0 = c * 64 + 32 * h;
+                    tmem_ld32(lane_taddr + n0, v);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float4 a0 = *reinterpret_cast<const float4*>(s_bfc2 + n0 + 8 * j);
+                        const float4 a1 = *reinterpret_cast<const float4*>(s_bfc2 + n0 + 8 * j + 4);
+                        const float4 g0 = *reinterpret_cast<const float4*>(s_gn + n0 + 8 * j);
+                        const float4 g1 = *reinterpret_cast<const float4*>(s_gn + n0 + 8 * j + 4);
+                        const float4 b0 = *reinterpret_cast<const float4*>(s_bn + n0 + 8 * j);
+                        const float4 b1 = *reinterpret_cast<const float4*>(s_bn + n0 + 8 * j + 4);
+                        uint4 o;
+                        o.x = pack2<F16>((v[8 * j] + a0.x - mean) * rstd * g0.x + b0.x, (v[8 * j + 1] + a0.y - mean) * rstd * g0.y + b0.y);
+                        o.y = pack2<F16>((v[8 * j + 2] + a0.z - mean) * rstd * g0.z + b0.z, (v[8 * j + 3] + a0.w - mean) * rstd * g0.w + b0.w);
+                        o.z = pack2<F16>((v[8 * j + 4] + a1.x - mean) * rstd * g1.x + b1.x, (v[8 * j + 5] + a1.y - mean) * rstd * g1.y + b1.y);
+                        o.w = pack2<F16>((v[8 * j + 6] + a1.z - mean) * rstd * g1.z + b1.z, (v[8 * j + 7] + a1.w - mean) * rstd * g1.w + b1.w);
+                        *reinterpret_cast<uint4*>(slot + slot_off(trow, 4 * h + j)) = o;
+                    }
+                }
+                fence_proxy_async_smem();
+                named_bar_sync(gbar, 128);
+                if (gleader && m0 < p.M) {
+                    tma_store_2d(&tmXN, slot, c * 64, m0);
+                    bulk_commit();
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(tfree_bar);
+            if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 11);
+        }
+        if (gleader) bulk_wait_all();
+        __syncwarp();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 2) tmem_dealloc<2>(tmem_base, 512);
+}
+
+}  // namespace ddc

@@ -15,6 +15,7 @@
 #include "common.cuh"
 #include "elementwise.cuh"
 #include "gemm2.cuh"
+#include "block_tail.cuh"
 
 using namespace ddc;
 
@@ -186,6 +187,47 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
     return launch_gemm2_inst<EPI, false, 1>(tmA, tmB, tmO, tmR, tmN, p, smem, st);
 }
 
+// ------------------------------------------------------------------------------- fused block tail launch
+static bool block_tail_usable(int M, int C, int bn_row) {
+    return C % 128 == 0 && C <= 384 && bn_row == 128 && (M + G2_BM - 1) / G2_BM >= 2 && !env_int("DDC_NO_FUSE", 0);
+}
+
+template <bool F16>
+static int launch_block_tail_inst(const CUtensorMap& tmO, const CUtensorMap& tmWp, const CUtensorMap& tmW1,
+                                  const CUtensorMap& tmW2, const CUtensorMap& tmXld, const CUtensorMap& tmXst,
+                                  const CUtensorMap& tmXN, BlockTailParams p, cudaStream_t st) {
+    static int attr_dev_mask = 0;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    auto kern = block_tail_kernel<F16>;
+    if (!(attr_dev_mask & (1 << dev))) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_dev_mask |= (1 << dev);
+    }
+    int stages = static_cast<int>((227 * 1024 - static_cast<long>(block_tail_smem_bytes(p.C, 0))) / (64 * 128));
+    if (stages > 8) stages = 8;
+    if (stages < 2) return fail(DDC_E_INVALID, "block tail: C=%d leaves no room for the weight ring", p.C);
+    p.stages = stages;
+    p.num_tiles = ((p.M + G2_BM - 1) / G2_BM + 1) / 2 * 2;
+    const int sms = num_sms();
+    int grid = p.num_tiles < sms ? p.num_tiles : sms;
+    grid = grid / 2 * 2;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(BT_THREADS);
+    cfg.dynamicSmemBytes = block_tail_smem_bytes(p.C, stages);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CK(cudaLaunchKernelEx(&cfg, kern, tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, p));
+    return DDC_OK;
+}
+
 // ------------------------------------------------------------------------------- attention launch
 static int att_pick_kc(int L) {
     const int cands[] = {128, 96, 80, 64, 48, 32};
@@ -246,6 +288,7 @@ struct LayerW {
     float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *b_qkv, *b_proj, *b_fc1, *b_fc2;
     bf16 *w_qkv, *w_proj, *w_fc1, *w_fc2;
     CUtensorMap tm_qkv[2], tm_proj[2], tm_fc1[2], tm_fc2[2];   // W tile boxes for cluster size 1 and 2
+    CUtensorMap tm_fc1_tail;                                  // fc1 as 64-row half tiles (fused block tail)
 };
 
 struct GraphKey {
@@ -438,6 +481,7 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
             mk(&l.tm_fc2[cs - 1], false, l.w_fc2, C, C, pl->bn_row / cs);
         }
     }
+    for (auto& l : pl->layers) mk(&l.tm_fc1_tail, false, l.w_fc1, C, C, 64);
     if (r != DDC_OK) {
         delete pl;
         return r;
@@ -469,7 +513,10 @@ extern "C" int ddc_plan_set_operand_format(ddc_plan* plan, int32_t fmt) {
 
 extern "C" int ddc_launches_per_step(const ddc_plan* plan) {
     if (plan == nullptr) return 0;
-    return 2 + 5 * plan->sh.depth + 2;   // patchify, embed GEMM, 5 per block, head GEMM, head_ddim
+    // patchify, embed GEMM, per block {qkv GEMM, attention, fused tail} or {qkv, attention, proj, fc1, fc2}, head GEMM,
+    // head_ddim (the fused tail needs at least two 128-row tiles; smaller calls fall back to the separate kernels)
+    const bool fused = block_tail_usable(plan->maxB * plan->L, plan->C, plan->bn_row);
+    return 2 + (fused ? 3 : 5) * plan->sh.depth + 2;
 }
 
 // ------------------------------------------------------------------------------- packing
@@ -595,6 +642,18 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
         MARK(KC_QKV);
         TRY(run_attention(pl->QKV, pl->O, B, L, C, s.heads, f16, st));
         MARK(KC_ATTN);
+        const float* lnn_g = (i + 1 < s.depth) ? pl->layers[i + 1].ln1_g : pl->lnf_g;
+        const float* lnn_b = (i + 1 < s.depth) ? pl->layers[i + 1].ln1_b : pl->lnf_b;
+        if (block_tail_usable(M, C, pl->bn_row)) {
+            BlockTailParams bt{};
+            bt.M = M; bt.C = C; bt.ln_eps = 1e-5f;
+            bt.b_proj = l.b_proj; bt.ln2_g = l.ln2_g; bt.ln2_b = l.ln2_b; bt.b_fc1 = l.b_fc1; bt.b_fc2 = l.b_fc2;
+            bt.lnn_g = lnn_g; bt.lnn_b = lnn_b;
+            if (f16) TRY((launch_block_tail_inst<true>(pl->tm_O, l.tm_proj[1], l.tm_fc1_tail, l.tm_fc2[1], pl->tm_Xld, pl->st_X, pl->st_XN, bt, st)));
+            else TRY((launch_block_tail_inst<false>(pl->tm_O, l.tm_proj[1], l.tm_fc1_tail, l.tm_fc2[1], pl->tm_Xld, pl->st_X, pl->st_XN, bt, st)));
+            MARK(KC_PROJ);
+            continue;
+        }
         Gemm2Params r{};
         r.M = M; r.N = C; r.K = C; r.bn = pl->bn_row; r.stages = pick_stages2(r.K, r.N, r.bn / cs, true);
         r.bias = l.b_proj; r.ln_g = l.ln2_g; r.ln_b = l.ln2_b; r.ln_eps = 1e-5f;
@@ -606,8 +665,8 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
         TRY((launch_gemm2<S_BF16_GELU>(pl->tm_XN, l.tm_fc1[cs - 1], pl->st_Hd, pl->tm_Xld, pl->st_XN, f, f16, cs, st)));
         MARK(KC_FC1);
         r.bias = l.b_fc2;
-        r.ln_g = (i + 1 < s.depth) ? pl->layers[i + 1].ln1_g : pl->lnf_g;
-        r.ln_b = (i + 1 < s.depth) ? pl->layers[i + 1].ln1_b : pl->lnf_b;
+        r.ln_g = lnn_g;
+        r.ln_b = lnn_b;
         TRY((launch_gemm2<R_RESID>(pl->tm_Hd, l.tm_fc2[cs - 1], pl->st_X, pl->tm_Xld, pl->st_XN, r, f16, cs, st)));
         MARK(KC_FC2);
     }
@@ -949,6 +1008,31 @@ extern "C" int ddc_k_gemm_resid_ln(int32_t fmt, int32_t M, int32_t C, int32_t K,
     p.M = M; p.N = C; p.K = K; p.bn = bn; p.stages = pick_stages2(K, C, bn / cs, true); p.bias = bias;
     p.ln_g = ln_g; p.ln_b = ln_b; p.ln_eps = 1e-5f;
     return launch_gemm2<R_RESID>(tmA, tmB, tmO, tmR, tmN, p, fmt == 1, cs, st);
+}
+
+extern "C" int ddc_k_block_tail(int32_t fmt, int32_t M, int32_t C, const void* O, const void* Wproj, const float* b_proj,
+                                const float* ln2_g, const float* ln2_b, const void* Wfc1, const float* b_fc1,
+                                const void* Wfc2, const float* b_fc2, const float* lnn_g, const float* lnn_b, float* x,
+                                void* xn, void* stream) {
+    if (!O || !Wproj || !b_proj || !ln2_g || !ln2_b || !Wfc1 || !b_fc1 || !Wfc2 || !b_fc2 || !lnn_g || !lnn_b || !x || !xn)
+        return fail(DDC_E_INVALID, "NULL tensor");
+    if (M < 129 || C % 128 != 0 || C > 384 || C <= 0)
+        return fail(DDC_E_INVALID, "block tail needs M > 128 and embed_dim in {128, 256, 384} (M=%d C=%d)", M, C);
+    const uint64_t Mp = (static_cast<uint64_t>(M) + G2_BM - 1) / G2_BM * G2_BM;
+    CUtensorMap tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN;
+    TRY(make_tmap(&tmO, false, O, Mp, C, G2_BM));
+    TRY(make_tmap(&tmWp, false, Wproj, C, C, 64));
+    TRY(make_tmap(&tmW1, false, Wfc1, C, C, 64));
+    TRY(make_tmap(&tmW2, false, Wfc2, C, C, 64));
+    TRY(make_tmap(&tmXld, true, x, Mp, C, G2_BM));
+    TRY(make_tmap(&tmXst, true, x, M, C, G2_BM));
+    TRY(make_tmap(&tmXN, false, xn, M, C, G2_BM));
+    BlockTailParams bt{};
+    bt.M = M; bt.C = C; bt.ln_eps = 1e-5f;
+    bt.b_proj = b_proj; bt.ln2_g = ln2_g; bt.ln2_b = ln2_b; bt.b_fc1 = b_fc1; bt.b_fc2 = b_fc2; bt.lnn_g = lnn_g; bt.lnn_b = lnn_b;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (fmt == 1) return launch_block_tail_inst<true>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, bt, st);
+    return launch_block_tail_inst<false>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, bt, st);
 }
 
 extern "C" int ddc_k_attention(int32_t fmt, const void* qkv, void* out, int32_t batch, int32_t L, int32_t C,

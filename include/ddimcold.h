@@ -158,6 +158,14 @@ int ddc_k_gemm(int32_t fmt, int32_t epi, int32_t M, int32_t N, int32_t K, const 
 int ddc_k_gemm_resid_ln(int32_t fmt, int32_t M, int32_t C, int32_t K, const void* A, const void* W, const float* bias, float* x,
                         const float* ln_g, const float* ln_b, void* xn, void* stream);
 
+/* Fused tail of a transformer block (reference ViT.py:136-137 with Mlp.forward :84-90 and the LayerNorm that
+ * follows, :133 / :212):  x += O Wproj^T + b_proj;  h = gelu_erf(LayerNorm2(x) Wfc1^T + b_fc1);
+ * x += h Wfc2^T + b_fc2 (fp32, in place);  xn = 16-bit LayerNorm_next(x).  O: 16-bit [m_pad, C]; W*: 16-bit [C, C];
+ * x: fp32 [m_pad, C]; xn: 16-bit [M, C]; C in {128, 256, 384}; M > 128. */
+int ddc_k_block_tail(int32_t fmt, int32_t M, int32_t C, const void* O, const void* Wproj, const float* b_proj,
+                     const float* ln2_g, const float* ln2_b, const void* Wfc1, const float* b_fc1, const void* Wfc2,
+                     const float* b_fc2, const float* lnn_g, const float* lnn_b, float* x, void* xn, void* stream);
+
 /* softmax(q k^T / sqrt(d)) v per (image, head) (reference ViT.py:107-114).
  * qkv: bf16 [B*L, 3C] (column s*C + head*d + e); out: bf16 [B*L, C]. */
 int ddc_k_attention(int32_t fmt, const void* qkv, void* out, int32_t batch, int32_t L, int32_t C, int32_t heads, void* stream);
