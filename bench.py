@@ -281,17 +281,34 @@ def main():
     flops_img_step = O.flops_per_image_step(sh)
     Cdim, L = sh.embed, sh.tokens
     M = B * L
-    # dominant kernel class: LN + qkv GEMM, algorithmic FLOPs 2*M*3C*C per launch
-    qkv_flops = 2.0 * M * 3 * Cdim * Cdim
-    qkv_ms = cls_ms[2] / max(1, cls_n[2])
-    achieved = qkv_flops / (qkv_ms * 1e-3) / 1e12
+    # algorithmic FLOPs per launch of each tensor-core class (2*M*N*K; attention 4*h*L^2*d per image)
+    heads = SHAPES[args.shape]["heads"]
+    fused_tail = cls_n[5] == 0 and cls_n[4] > 0          # proj + fc1 + fc2 run as one block-tail kernel
+    P = sh.patch_dim
+    cls_flops = {1: 2.0 * M * Cdim * P, 2: 2.0 * M * 3 * Cdim * Cdim, 3: 4.0 * B * L * L * Cdim,
+                 4: (6.0 if fused_tail else 2.0) * M * Cdim * Cdim, 5: 2.0 * M * Cdim * Cdim, 6: 2.0 * M * Cdim * Cdim,
+                 7: 2.0 * M * Cdim * P}
+    names = list(CLASS_NAMES)
+    if fused_tail:
+        names[4] = "block_tail(proj+ln+fc1+gelu+fc2+ln)"
     peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
     kernels = {}
     step_ms_sum = sum(cls_ms[i] for i in range(9)) / prof_steps
-    for i, name in enumerate(CLASS_NAMES):
+    for i, name in enumerate(names):
         if cls_n[i]:
-            kernels[name] = {"launches_per_step": cls_n[i] // prof_steps, "ms_per_launch": cls_ms[i] / cls_n[i],
+            ms = cls_ms[i] / cls_n[i]
+            kernels[name] = {"launches_per_step": cls_n[i] // prof_steps, "ms_per_launch": ms,
                              "share": (cls_ms[i] / prof_steps) / step_ms_sum}
+            if i in cls_flops:
+                kernels[name]["tflops"] = cls_flops[i] / (ms * 1e-3) / 1e12
+    # roofline object: the kernel class with the largest share of the step (tensor-bound: dense contractions)
+    dom = max((i for i in (2, 4) if cls_n[i]), key=lambda i: cls_ms[i])
+    dom_ms = cls_ms[dom] / cls_n[dom]
+    dom_flops = cls_flops[dom]
+    achieved = dom_flops / (dom_ms * 1e-3) / 1e12
+    dom_name = {2: "gemm2_kernel<S_BF16> (qkv GEMM, tcgen05 cta_group::2)",
+                4: "block_tail_kernel (proj + LN2 + fc1 + GELU + fc2 + LN, tcgen05 cta_group::2)" if fused_tail
+                   else "gemm2_kernel<R_RESID> (proj GEMM + residual + LN)"}[dom]
     whole_tf = flops_img_step * B * n_steps * args.steps * world / (dev_ms / 1e3) / 1e12 / world
     line = {
         "metric": f"DDIM images/sec (N={B}/GPU, k={k})", "value": value, "unit": "images/s", "n_gpus": world,
@@ -310,10 +327,11 @@ def main():
                 "note": "N>1: each rank uploads its own x_T; one NCCL gather to rank 0, which reads all images back"},
         "gpu_launches": launches_per_pass * args.steps,
         "clocks": clk,
-        "roofline": {"bound": "tensor", "kernel": "gemm_umma_kernel<A_LN,EPI_BF16> (LayerNorm + qkv GEMM)",
+        "roofline": {"bound": "tensor", "kernel": dom_name,
                      "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
                      "traffic": None, "peak_source": f"{pk_src} bf16 sustained (MEASURED_PEAKS.json)",
-                     "flops_per_launch": qkv_flops, "ms_per_launch": qkv_ms},
+                     "flops_per_launch": dom_flops, "ms_per_launch": dom_ms,
+                     "share_of_step": (cls_ms[dom] / prof_steps) / step_ms_sum},
         "kernels": kernels,
     }
     if not args.no_cpu_baseline:

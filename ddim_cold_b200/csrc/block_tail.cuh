@@ -17,9 +17,9 @@
 //          W ring            64-row halves of 128 x 64 weight tiles, streamed in MMA order
 //
 //   MMA order   proj(n = 0..NB-1) | for j: fc1(j) ; fc2 partial(j): X1[:, n-tile] += H_j * Wfc2[n-tile, j-th K range]
-//   epilogue    epi1: + residual + bias -> TMEM, exact two-pass LayerNorm2 -> Abuf
+//   epilogue    epi1: + residual + bias -> TMEM, LayerNorm2 (shifted one-pass statistics, pairwise merge) -> Abuf
 //               epi2(j): + bias, GELU -> Hbuf[j & 1]
-//               epi3: + bias -> X (TMA store), exact two-pass LayerNorm_next -> XN (TMA store)
+//               epi3: + bias -> X (TMA store), LayerNorm_next -> XN (TMA store)
 #pragma once
 
 #include "common.cuh"
@@ -263,26 +263,25 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         const float* oth_sq = red + 256 + (hf ^ 1) * 128 + trow;
         uint32_t tc = 0, g = 0, ri = 0, res_phase = 0;
 
-        // exact two-pass LayerNorm statistics of the row held in TMEM (+ `add`), shared between the two groups
-        auto row_stats = [&](float sum, const float* add, float& mean, float& rstd) {
-            *red_sum = sum;
-            tc_fence_before();
+        // LayerNorm statistics in one pass over the data: each group accumulates sum and sum of squares of its half of
+        // the row around a shift K (the first value it sees, so nothing cancels), turns them into (mean, M2) of that
+        // half, and the halves are merged with the exact pairwise update (Chan et al.): equal counts n = C/2,
+        // mean = (m0 + m1)/2, M2 = M2_0 + M2_1 + n/2 (m0 - m1)^2.
+        const float half_n = 0.5f * static_cast<float>(C);
+        auto row_stats = [&](float shift, float s1, float s2, float& mean, float& rstd) {
+            const float mg = shift + s1 / half_n;
+            const float m2g = s2 - s1 * s1 / half_n;
+            *red_sum = mg;
+            *red_sq = m2g;
+            tc_fence_before();                  // the partner group later reads TMEM columns this warp stored
             named_bar_sync(3 + q, 64);
             tc_fence_after();
-            mean = (sum + *oth_sum) * inv_c;
-            float sq = 0.f;
-            for (int c = hf; c < nchunk; c += 2) {
-                float v[32];
-                tmem_ld32(lane_taddr + c * 32, v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const float d = v[i] + (add ? add[c * 32 + i] : 0.f) - mean;
-                    sq += d * d;
-                }
-            }
-            *red_sq = sq;
-            named_bar_sync(3 + q, 64);
-            rstd = rsqrtf((sq + *oth_sq) * inv_c + p.ln_eps);
+            const float mo = *oth_sum, m2o = *oth_sq;
+            mean = 0.5f * (mg + mo);
+            const float d = mg - mo;
+            const float m2 = m2g + m2o + 0.5f * half_n * d * d;
+            rstd = rsqrtf(m2 * inv_c + p.ln_eps);
+            named_bar_sync(3 + q, 64);          // both partners have read the exchange slots before they are reused
         };
 
         if (gleader && first_tile < p.num_tiles)
@@ -300,7 +299,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 tma_load_2d(gslots + s * G2_GSLOT_BYTES, &tmXld, &my_res[s], hf * 32, m0);
             }
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 0);
-            float sum = 0.f;
+            float shift = 0.f, s1 = 0.f, s2 = 0.f;
             int waited = -1;
             for (int c = hf; c < nchunk; c += 2, ++ri) {
                 const uint32_t s = ri & 1u;
@@ -327,14 +326,19 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     v[4 * j] += r.x + b.x; v[4 * j + 1] += r.y + b.y;
                     v[4 * j + 2] += r.z + b.z; v[4 * j + 3] += r.w + b.w;
                 }
+                if (c == hf) shift = v[0];
 #pragma unroll
-                for (int i = 0; i < 32; ++i) sum += v[i];
+                for (int i = 0; i < 32; ++i) {
+                    const float d = v[i] - shift;
+                    s1 += d;
+                    s2 = fmaf(d, d, s2);
+                }
                 tmem_st32(lane_taddr + n0, v);
                 named_bar_sync(gbar, 128);         // every warp of the group has read the slot before it is refilled
             }
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 1);
             float mean, rstd;
-            row_stats(sum, nullptr, mean, rstd);
+            row_stats(shift, s1, s2, mean, rstd);
             // LayerNorm2 -> Abuf (K-major, 128-byte swizzle: 64 columns = one K block).  All proj MMAs that read
             // the O tile in Abuf completed before proj_bar[NB-1] fired.
             for (int c = hf; c < C / 64; c += 2) {
@@ -409,7 +413,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             mbar_wait(final_bar, tc & 1);
             tc_fence_after();
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 9);
-            sum = 0.f;
+            s1 = 0.f; s2 = 0.f;
             for (int c = hf; c < nchunk; c += 2, ++ri) {
                 uint8_t* slot = gslots + (ri & 1u) * G2_GSLOT_BYTES;
                 if (gleader) bulk_wait_read<1>();
@@ -424,8 +428,13 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     *reinterpret_cast<float4*>(slot + slot_off(trow, j)) =
                         make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                 }
+                if (c == hf) shift = v[0];
 #pragma unroll
-                for (int i = 0; i < 32; ++i) sum += v[i];
+                for (int i = 0; i < 32; ++i) {
+                    const float d = v[i] - shift;
+                    s1 += d;
+                    s2 = fmaf(d, d, s2);
+                }
                 fence_proxy_async_smem();
                 named_bar_sync(gbar, 128);
                 if (gleader && m0 < p.M) {
@@ -434,7 +443,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 }
             }
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 10);
-            row_stats(sum, s_bfc2, mean, rstd);
+            row_stats(shift, s1, s2, mean, rstd);
             for (int c = hf; c < C / 64; c += 2, ++ri) {
                 uint8_t* slot = gslots + (ri & 1u) * G2_GSLOT_BYTES;
                 if (gleader) bulk_wait_read<1>();

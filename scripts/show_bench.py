@@ -5,4 +5,4 @@ for f in sys.argv[1:]:
     if 'e2e' in d: print('  e2e', round(d['e2e']['value'], 1))
     if 'roofline' in d: print('  roofline', round(d['roofline']['achieved'], 1), round(d['roofline']['frac'], 3))
     for k, v in d.get('kernels', {}).items():
-        print('    %-14s n=%d  %.4f ms  share %.3f' % (k, v['launches_per_step'], v['ms_per_launch'], v['share']))
+        print('    %-38s n=%d  %.4f ms  share %.3f  %s' % (k, v['launches_per_step'], v['ms_per_launch'], v['share'], ('%.0f TF' % v['tflops']) if 'tflops' in v else ''))
