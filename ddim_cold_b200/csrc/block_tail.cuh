@@ -14,7 +14,7 @@
 //   smem   Abuf  KB x 16 KB  O tile (TMA), later overwritten by LayerNorm2(X1) in the same swizzled K-major layout
 //          Hbuf  2 x 32 KB   one hidden block of H each (two K blocks); doubles as staging for residual loads
 //                            (phase 1) and for the X / XN stores (phase 3) while no hidden block is live
-//          W ring            64-row halves of 128 x 64 weight tiles, streamed in MMA order
+//          W ring            64-row halves of 128 x 64 weight tiles, gk K blocks per stage, streamed in MMA order
 //
 //   MMA order   proj(n = 0..NB-1) | for j: fc1(j) ; fc2 partial(j): X1[:, n-tile] += H_j * Wfc2[n-tile, j-th K range]
 //   epilogue    epi1: + residual + bias -> TMEM, LayerNorm2 (shifted one-pass statistics, pairwise merge) -> Abuf
@@ -33,6 +33,7 @@ constexpr int BT_HSLOT_BYTES = 2 * G2_A_KB_BYTES;   // one hidden block: 128 row
 
 struct BlockTailParams {
     int M, C, stages, num_tiles;
+    int gk;                  // K blocks (of 64) per W ring stage: 1 or 2.  One handshake moves gk * 8 KB per CTA.
     const float* b_proj;
     const float* ln2_g;
     const float* ln2_b;
@@ -41,15 +42,17 @@ struct BlockTailParams {
     const float* lnn_g;      // LayerNorm that follows the block (next block's norm1, or the final norm)
     const float* lnn_b;
     float ln_eps;
-    long long* dbg;          // probes only: [role 2][64] SM clock stamps of CTA 0
+    long long* dbg;          // probes only: [role 2][64] SM clock stamps of CTA 0, [128..] wait accounting
+    int flags;               // probes only: bit 0 = L2-prefetch the next tile's O / residual rows (measured: no gain)
+    int stagger;             // SM cycles by which CTA pairs with a spare round start late (0 = off), see the kernel
 };
 
 __device__ __forceinline__ void bt_stamp(const BlockTailParams& p, int role, int idx) {
     if (p.dbg != nullptr && blockIdx.x == 0 && idx < 64) p.dbg[role * 64 + idx] = clock64();
 }
 
-inline size_t block_tail_smem_bytes(int C, int stages) {
-    return 1024 + static_cast<size_t>(C / 64) * G2_A_KB_BYTES + 2 * BT_HSLOT_BYTES + static_cast<size_t>(stages) * 64 * 128 +
+inline size_t block_tail_smem_bytes(int C, int stages, int gk) {
+    return 1024 + static_cast<size_t>(C / 64) * G2_A_KB_BYTES + 2 * BT_HSLOT_BYTES + static_cast<size_t>(stages) * gk * 64 * 128 +
            ((static_cast<size_t>(7) * C * 4 + 127) & ~static_cast<size_t>(127)) + G2_TAIL_BYTES;
 }
 
@@ -70,7 +73,9 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     const int C = p.C;
     const int KB = C / 64;                       // K blocks of every GEMM (K == C)
     const int NB = C / BT_BN;                    // N tiles == hidden blocks
-    constexpr uint32_t kStageBytes = 64 * 128;   // this CTA's half (64 rows) of a 128 x 64 weight tile
+    constexpr uint32_t kWBytes = 64 * 128;       // this CTA's half (64 rows) of a 128 x 64 weight tile
+    const uint32_t gk = static_cast<uint32_t>(p.gk);
+    const uint32_t kStageBytes = gk * kWBytes;   // a ring stage: gk consecutive K blocks of one N tile
     uint8_t* abuf = smem;
     uint8_t* hbuf = abuf + static_cast<size_t>(KB) * G2_A_KB_BYTES;
     uint8_t* ring = hbuf + 2 * BT_HSLOT_BYTES;
@@ -82,13 +87,13 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     uint64_t* afull_bar = bars + 16;      // [8]  O K block landed              (leader)
     uint64_t* aempty_bar = bars + 24;     // [1]  Abuf no longer read by fc1    (pair commit)
     uint64_t* proj_bar = bars + 25;       // [4]  proj N tile complete          (pair commit)
-    uint64_t* ln2_bar = bars + 29;        // [1]  LayerNorm2 output in Abuf     (leader, 8 warps x 2 CTAs)
+    uint64_t* ln2_bar = bars + 56;        // [8]  LayerNorm2 K block in Abuf    (leader, 4 warps x 2 CTAs)
     uint64_t* t1full_bar = bars + 30;     // [1]  fc1 accumulator complete      (pair commit)
     uint64_t* t1free_bar = bars + 31;     // [1]  fc1 accumulator drained       (leader, 16 arrivals)
     uint64_t* hready_bar = bars + 32;     // [2]  hidden block written          (leader, 16 arrivals)
     uint64_t* hfree_bar = bars + 34;      // [2]  hidden block consumed by fc2  (pair commit)
     uint64_t* final_bar = bars + 36;      // [1]  row block holds X1 + H Wfc2^T (pair commit)
-    uint64_t* tfree_bar = bars + 37;      // [1]  row block drained by epi3     (leader, 16 arrivals)
+    uint64_t* tfree_bar = bars + 42;      // [4]  N tile of the row block drained by epi3 (leader, 16 arrivals)
     uint64_t* res_bar = bars + 38;        // [4]  residual chunk landed (group x slot)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 48);
     float* red = reinterpret_cast<float*>(bars + 64);     // [2 stats][2 groups][128 rows]
@@ -110,7 +115,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         }
         mbar_init(aempty_bar, 1);
         for (int i = 0; i < 4; ++i) mbar_init(&proj_bar[i], 1);
-        mbar_init(ln2_bar, 16);
+        for (int i = 0; i < 8; ++i) mbar_init(&ln2_bar[i], 8);
         mbar_init(t1full_bar, 1);
         mbar_init(t1free_bar, 16);
         mbar_init(&hready_bar[0], 16);
@@ -118,7 +123,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         mbar_init(&hfree_bar[0], 1);
         mbar_init(&hfree_bar[1], 1);
         mbar_init(final_bar, 1);
-        mbar_init(tfree_bar, 16);
+        for (int i = 0; i < 4; ++i) mbar_init(&tfree_bar[i], 16);
         for (int i = 0; i < 4; ++i) mbar_init(&res_bar[i], 1);
         fence_barrier_init();
     }
@@ -135,6 +140,19 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // Phase stagger.  Every pair walks the same phases per tile -- HBM reads (O, residual), an MLP stretch that moves no
+    // activation bytes, HBM writes (X, XN) -- and with all pairs in lockstep the memory system sees bursts it cannot
+    // absorb followed by idle time.  When the tile count does not divide evenly, the pairs that run one round fewer
+    // have a whole tile of slack: they start `stagger` cycles late (a good part of a tile), so their bursts fall into the
+    // other pairs' quiet stretch.  Costs nothing: they still finish before the pairs with the extra round.
+    if (p.stagger > 0) {
+        const int my_rounds = (p.num_tiles - first_tile + tile_step - 1) / tile_step;
+        const int max_rounds = (p.num_tiles + tile_step - 1) / tile_step;
+        if (my_rounds < max_rounds) {
+            const long long t0 = clock64();
+            while (clock64() - t0 < p.stagger) __nanosleep(256);
+        }
+    }
     const float* s_bproj = sp;
     const float* s_g2 = sp + C;
     const float* s_b2 = sp + 2 * C;
@@ -154,8 +172,9 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     const uint32_t phase = (bit / static_cast<uint32_t>(p.stages)) & 1u;
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * kStageBytes);
-                    tma_load_2d_pair(ring + static_cast<size_t>(stage) * kStageBytes, tm, &full_bar[stage], kcol,
-                                     row0 + static_cast<int>(crank) * 64);
+                    for (uint32_t i = 0; i < gk; ++i)
+                        tma_load_2d_pair(ring + static_cast<size_t>(stage) * kStageBytes + i * kWBytes, tm, &full_bar[stage],
+                                         kcol + static_cast<int>(i) * 64, row0 + static_cast<int>(crank) * 64);
                 }
                 ++bit;
             };
@@ -166,14 +185,20 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     if (leader) mbar_arrive_expect_tx(&afull_bar[kb], 2 * G2_A_KB_BYTES);
                     tma_load_2d_pair(abuf + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmO, &afull_bar[kb], kb * 64, m0);
                 }
-                if (me == 0 && tile + tile_step < p.num_tiles)       // next tile's O rows -> L2
-                    for (int kb = 0; kb < KB; ++kb) tma_prefetch_l2_2d(&tmO, kb * 64, (tile + tile_step) * G2_BM);
                 for (int n = 0; n < NB; ++n)
-                    for (int kb = 0; kb < KB; ++kb) load_w(&tmWp, kb * 64, n * BT_BN);
+                    for (int kb = 0; kb < KB; kb += p.gk) load_w(&tmWp, kb * 64, n * BT_BN);
+                // MMA order of the MLP: fc1(0) | fc1(j+1), fc2 partial(j) ...  (fc1 of the next hidden block runs
+                // while the epilogue applies GELU to the current one)
+                for (int kb = 0; kb < KB; kb += p.gk) load_w(&tmW1, kb * 64, 0);
+                // The tile's own HBM reads (O, residual) are over by now and its stores have not begun: pull the next
+                // tile's O rows into L2 in this quiet window rather than on top of the current tile's loads.
+                if (me == 0 && tile + tile_step < p.num_tiles && (p.flags & 1))
+                    for (int kb = 0; kb < KB; ++kb) tma_prefetch_l2_2d(&tmO, kb * 64, (tile + tile_step) * G2_BM);
                 for (int j = 0; j < NB; ++j) {
-                    for (int kb = 0; kb < KB; ++kb) load_w(&tmW1, kb * 64, j * BT_BN);
+                    if (j + 1 < NB)
+                        for (int kb = 0; kb < KB; kb += p.gk) load_w(&tmW1, kb * 64, (j + 1) * BT_BN);
                     for (int n = 0; n < NB; ++n)
-                        for (int kk = 0; kk < 2; ++kk) load_w(&tmW2, (2 * j + kk) * 64, n * BT_BN);
+                        for (int kk = 0; kk < 2; kk += p.gk) load_w(&tmW2, (2 * j + kk) * 64, n * BT_BN);
                 }
             }
         }
@@ -185,7 +210,8 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         const uint64_t ad0 = umma_desc_sw128(smem_u32(abuf));
         const uint64_t hd0 = umma_desc_sw128(smem_u32(hbuf));
         const uint64_t bd0 = umma_desc_sw128(smem_u32(ring));
-        constexpr uint32_t kStageUnits = kStageBytes >> 4;
+        const uint32_t kStageUnits = kStageBytes >> 4;
+        constexpr uint32_t kWUnits = kWBytes >> 4;
         constexpr uint32_t kKbUnits = G2_A_KB_BYTES >> 4;
         uint32_t bit = 0, tc = 0, g = 0;          // g: running hidden-block index (H slot = g & 1)
         auto mma_step = [&](uint32_t d_tmem, uint64_t adesc, uint32_t accumulate) {
@@ -195,46 +221,60 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             tc_fence_after();
             if (elect_one()) {
                 umma_kblock<2>(d_tmem, adesc, bd0 + static_cast<uint64_t>(stage * kStageUnits), idesc, accumulate);
+                if (gk == 2)
+                    umma_kblock<2>(d_tmem, adesc + kKbUnits, bd0 + static_cast<uint64_t>(stage * kStageUnits + kWUnits), idesc, 1u);
                 umma_commit_pair(&empty_bar[stage]);
             }
             __syncwarp();
             ++bit;
         };
         for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tc) {
-            mbar_wait(tfree_bar, (tc & 1) ^ 1);                      // epi3 of the previous tile has drained TMEM
-            tc_fence_after();
             if (lane == 0) bt_stamp(p, 0, tc * 16 + 0);
-            // ---- proj: row block <- O * Wproj^T
+            // ---- proj: row block <- O * Wproj^T.  N tile n may start as soon as epi3 of the previous tile has
+            // drained columns [128 n, 128 n + 128).
             for (int n = 0; n < NB; ++n) {
-                for (int kb = 0; kb < KB; ++kb) {
-                    if (n == 0) { mbar_wait(&afull_bar[kb], tc & 1); tc_fence_after(); }
+                mbar_wait(&tfree_bar[n], (tc & 1) ^ 1);
+                tc_fence_after();
+                for (int kb = 0; kb < KB; kb += p.gk) {
+                    if (n == 0) {
+                        mbar_wait(&afull_bar[kb], tc & 1);
+                        if (gk == 2) mbar_wait(&afull_bar[kb + 1], tc & 1);
+                        tc_fence_after();
+                    }
                     mma_step(tb + static_cast<uint32_t>(n * BT_BN), ad0 + static_cast<uint64_t>(kb * kKbUnits), kb != 0);
                 }
                 if (elect_one()) umma_commit_pair(&proj_bar[n]);
                 __syncwarp();
             }
             if (lane == 0) bt_stamp(p, 0, tc * 16 + 1);
-            // ---- MLP: Abuf now receives LayerNorm2(X1) from the epilogue warps of both CTAs
-            mbar_wait(ln2_bar, tc & 1);
-            tc_fence_after();
-            if (lane == 0) bt_stamp(p, 0, tc * 16 + 2);
-            for (int j = 0; j < NB; ++j, ++g) {
-                const uint32_t hs = g & 1u;
-                mbar_wait(t1free_bar, (g & 1u) ^ 1u);                 // fc1 accumulator drained by epi2(g - 1)
+            // ---- MLP: Abuf now receives LayerNorm2(X1) from the epilogue warps of both CTAs, K block by K block
+            auto fc1 = [&](int j, uint32_t gj, bool first) {
+                mbar_wait(t1free_bar, (gj & 1u) ^ 1u);                // fc1 accumulator read out by epi2(gj - 1)
                 tc_fence_after();
-                for (int kb = 0; kb < KB; ++kb)
+                for (int kb = 0; kb < KB; kb += p.gk) {
+                    if (first) {
+                        mbar_wait(&ln2_bar[kb], tc & 1);
+                        if (gk == 2) mbar_wait(&ln2_bar[kb + 1], tc & 1);
+                        tc_fence_after();
+                    }
                     mma_step(tb + static_cast<uint32_t>(C), ad0 + static_cast<uint64_t>(kb * kKbUnits), kb != 0);
-                if (lane == 0) bt_stamp(p, 0, tc * 16 + 3 + 4 * j);
+                }
                 if (elect_one()) {
                     umma_commit_pair(t1full_bar);
                     if (j == NB - 1) umma_commit_pair(aempty_bar);  // Abuf may take the next tile's O
                 }
                 __syncwarp();
+                if (lane == 0) bt_stamp(p, 0, tc * 16 + 3 + 4 * j);
+            };
+            fc1(0, g, true);
+            for (int j = 0; j < NB; ++j, ++g) {
+                const uint32_t hs = g & 1u;
+                if (j + 1 < NB) fc1(j + 1, g + 1, false);
                 mbar_wait(&hready_bar[hs], (g >> 1) & 1u);            // epi2 wrote hidden block g into Hbuf[hs]
                 tc_fence_after();
                 if (lane == 0) bt_stamp(p, 0, tc * 16 + 4 + 4 * j);
                 for (int n = 0; n < NB; ++n)
-                    for (int kk = 0; kk < 2; ++kk)
+                    for (int kk = 0; kk < 2; kk += p.gk)
                         mma_step(tb + static_cast<uint32_t>(n * BT_BN),
                                  hd0 + static_cast<uint64_t>(hs * (BT_HSLOT_BYTES >> 4) + kk * kKbUnits), 1u);
                 if (lane == 0) bt_stamp(p, 0, tc * 16 + 5 + 4 * j);
@@ -288,27 +328,23 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             for (int c = hf; c < nchunk; c += 2) tma_prefetch_l2_2d(&tmXld, c * 32, first_tile * G2_BM);
         for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tc) {
             const int m0 = tile * G2_BM;
-            if (gleader && tile + tile_step < p.num_tiles)
-                for (int c = hf; c < nchunk; c += 2) tma_prefetch_l2_2d(&tmXld, c * 32, (tile + tile_step) * G2_BM);
 
             // ------------------------------------------------------------ epi1: X1 = acc + b_proj + X -> TMEM
             if (gleader) {
                 bulk_wait_read<0>();               // the previous tile's X / XN stores have read the staging slots
-                const uint32_t s = ri & 1u;
-                mbar_arrive_expect_tx(&my_res[s], G2_GSLOT_BYTES);
-                tma_load_2d(gslots + s * G2_GSLOT_BYTES, &tmXld, &my_res[s], hf * 32, m0);
+                for (int i = 0; i < 2 && hf + 2 * i < nchunk; ++i) {      // both slots in flight from the start
+                    const uint32_t s = (ri + i) & 1u;
+                    mbar_arrive_expect_tx(&my_res[s], G2_GSLOT_BYTES);
+                    tma_load_2d(gslots + s * G2_GSLOT_BYTES, &tmXld, &my_res[s], (hf + 2 * i) * 32, m0);
+                }
             }
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 0);
             float shift = 0.f, s1 = 0.f, s2 = 0.f;
             int waited = -1;
+            long long res_wait = 0;                // probes only: cycles this warp waited for residual chunks
             for (int c = hf; c < nchunk; c += 2, ++ri) {
                 const uint32_t s = ri & 1u;
                 uint8_t* slot = gslots + s * G2_GSLOT_BYTES;
-                if (gleader && c + 2 < nchunk) {   // the other slot was fully consumed one iteration ago (no stores here)
-                    const uint32_t s2 = s ^ 1u;
-                    mbar_arrive_expect_tx(&my_res[s2], G2_GSLOT_BYTES);
-                    tma_load_2d(gslots + s2 * G2_GSLOT_BYTES, &tmXld, &my_res[s2], (c + 2) * 32, m0);
-                }
                 const int n0 = c * 32;
                 if (n0 / BT_BN != waited) {
                     waited = n0 / BT_BN;
@@ -317,7 +353,9 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 }
                 float v[32];
                 tmem_ld32(lane_taddr + n0, v);
+                const long long w0 = (p.dbg != nullptr) ? clock64() : 0;
                 mbar_wait(&my_res[s], (res_phase >> s) & 1);
+                if (p.dbg != nullptr) res_wait += clock64() - w0;
                 res_phase ^= (1u << s);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
@@ -335,8 +373,15 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 }
                 tmem_st32(lane_taddr + n0, v);
                 named_bar_sync(gbar, 128);         // every warp of the group has read the slot before it is refilled
+                if (gleader && c + 4 < nchunk) {   // two loads per group stay in flight: each has two iterations to land
+                    mbar_arrive_expect_tx(&my_res[s], G2_GSLOT_BYTES);
+                    tma_load_2d(slot, &tmXld, &my_res[s], (c + 4) * 32, m0);
+                }
             }
-            if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 1);
+            if (warp == 4 && lane == 0) {
+                bt_stamp(p, 1, tc * 16 + 1);
+                if (p.dbg != nullptr && blockIdx.x == 0 && tc < 4) p.dbg[128 + tc] = res_wait;
+            }
             float mean, rstd;
             row_stats(shift, s1, s2, mean, rstd);
             // LayerNorm2 -> Abuf (K-major, 128-byte swizzle: 64 columns = one K block).  All proj MMAs that read
@@ -362,12 +407,16 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                         *reinterpret_cast<uint4*>(kblk + slot_off(trow, 4 * h + j)) = o;
                     }
                 }
+                fence_proxy_async_smem();          // generic writes -> visible to the tensor core's operand reads
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_leader(&ln2_bar[c]);    // fc1 can consume this K block right away
             }
-            fence_proxy_async_smem();              // generic writes -> visible to the tensor core's operand reads
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_leader(ln2_bar);
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 2);
+
+            // the MLP phase moves no activation bytes: the quiet window for the next tile's residual rows -> L2
+            if (gleader && tile + tile_step < p.num_tiles && (p.flags & 1))
+                for (int c = hf; c < nchunk; c += 2) tma_prefetch_l2_2d(&tmXld, c * 32, (tile + tile_step) * G2_BM);
 
             // ------------------------------------------------------------ epi2(j): H_j = gelu(acc + b_fc1) -> Hbuf
             for (int j = 0; j < NB; ++j, ++g) {
@@ -378,11 +427,18 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 if (g >= 2) mbar_wait(&hfree_bar[hs], ((g >> 1) & 1u) ^ 1u);   // fc2 partial(g-2) has read this slot
                 // group hf converts hidden columns [64*hf, +64) of the block = K block hf of the slot
                 uint8_t* kblk = hbuf + static_cast<size_t>(hs) * BT_HSLOT_BYTES + static_cast<size_t>(hf) * G2_A_KB_BYTES;
+                // read this thread's 64 accumulator columns, then hand the accumulator back at once: fc1 of the next
+                // hidden block overlaps the GELU below
+                float vv[2][32];
+                tmem_ld32(lane_taddr + static_cast<uint32_t>(C) + hf * 64, vv[0]);
+                tmem_ld32(lane_taddr + static_cast<uint32_t>(C) + hf * 64 + 32, vv[1]);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_leader(t1free_bar);
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    float v[32];
+                    float (&v)[32] = vv[h];
                     const int c0 = hf * 64 + 32 * h;
-                    tmem_ld32(lane_taddr + static_cast<uint32_t>(C) + c0, v);
 #pragma unroll
                     for (int i = 0; i < 32; i += 4) {
                         const float4 b = *reinterpret_cast<const float4*>(s_bfc1 + j * BT_BN + c0 + i);
@@ -402,10 +458,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 fence_proxy_async_smem();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) {
-                    mbar_arrive_leader(&hready_bar[hs]);
-                    mbar_arrive_leader(t1free_bar);
-                }
+                if (lane == 0) mbar_arrive_leader(&hready_bar[hs]);
                 if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 4 + 2 * j);
             }
 
@@ -469,6 +522,11 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                         *reinterpret_cast<uint4*>(slot + slot_off(trow, 4 * h + j)) = o;
                     }
                 }
+                // groups 0 / 1 hold the two 64-column halves of N tile c / 2: once both are read out, the next tile's
+                // proj may overwrite those TMEM columns while the remaining N tiles are still being normalised
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_leader(&tfree_bar[c >> 1]);
                 fence_proxy_async_smem();
                 named_bar_sync(gbar, 128);
                 if (gleader && m0 < p.M) {
@@ -476,9 +534,6 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     bulk_commit();
                 }
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_leader(tfree_bar);
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 11);
         }
         if (gleader) bulk_wait_all();

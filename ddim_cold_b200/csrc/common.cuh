@@ -354,7 +354,8 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
 __device__ __forceinline__ float gelu_erf(float x) {
     const float hx = 0.5f * x;
     const float ha = fabsf(hx);
-    const float t = __fdividef(1.0f, fmaf(ha, 0.47047f * 1.41421356237f, 1.0f));
+    float t;                                       // 1 / (1 + p |x| / sqrt 2): the argument is in [1, inf), one MUFU does
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(ha, 0.47047f * 1.41421356237f, 1.0f)));
     const float poly = t * fmaf(t, fmaf(t, 0.7478556f, -0.0958798f), 0.3480242f);
     float e;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(hx * hx * -2.88539008178f));   // exp(-x^2/2) = 2^(-(x/2)^2 * 4 * log2(e)/2)

@@ -204,7 +204,12 @@ static int launch_block_tail_inst(const CUtensorMap& tmO, const CUtensorMap& tmW
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_dev_mask |= (1 << dev);
     }
-    int stages = static_cast<int>((227 * 1024 - static_cast<long>(block_tail_smem_bytes(p.C, 0))) / (64 * 128));
+    // Two K blocks per ring stage: the stage handshake (full barrier -> MMA -> pair commit -> empty barrier) costs about
+    // 500 cycles whatever it carries (scripts/probes/pair_ring_probe.cu), so 16 KB stages stream W twice as fast as 8 KB.
+    p.gk = env_int("DDC_TAIL_GK", 2) == 1 ? 1 : 2;
+    p.flags = env_int("DDC_TAIL_FLAGS", 0);
+    p.stagger = env_int("DDC_TAIL_STAGGER", 115 * p.C);      // ~3/4 of a tile in SM cycles (measured ~58k per tile at C = 384)
+    int stages = static_cast<int>((227 * 1024 - static_cast<long>(block_tail_smem_bytes(p.C, 0, 1))) / (p.gk * 64 * 128));
     if (stages > 8) stages = 8;
     if (stages < 2) return fail(DDC_E_INVALID, "block tail: C=%d leaves no room for the weight ring", p.C);
     p.stages = stages;
@@ -215,7 +220,7 @@ static int launch_block_tail_inst(const CUtensorMap& tmO, const CUtensorMap& tmW
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(BT_THREADS);
-    cfg.dynamicSmemBytes = block_tail_smem_bytes(p.C, stages);
+    cfg.dynamicSmemBytes = block_tail_smem_bytes(p.C, stages, p.gk);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;

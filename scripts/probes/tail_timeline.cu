@@ -6,7 +6,7 @@ int main() {
     const size_t Mp = (M + 127) / 128 * 128;
     void *O, *Wp, *W1, *W2, *XN; float *X, *v; long long* dbg;
     cudaMalloc(&O, Mp * C * 2); cudaMalloc(&Wp, C * C * 2); cudaMalloc(&W1, C * C * 2); cudaMalloc(&W2, C * C * 2);
-    cudaMalloc(&XN, Mp * C * 2); cudaMalloc(&X, Mp * C * 4); cudaMalloc(&v, C * 4); cudaMalloc(&dbg, 2 * 64 * 8);
+    cudaMalloc(&XN, Mp * C * 2); cudaMalloc(&X, Mp * C * 4); cudaMalloc(&v, C * 4); cudaMalloc(&dbg, 3 * 64 * 8);
     cudaMemset(O, 0, Mp * C * 2); cudaMemset(Wp, 0, C * C * 2); cudaMemset(W1, 0, C * C * 2); cudaMemset(W2, 0, C * C * 2);
     cudaMemset(X, 0, Mp * C * 4); cudaMemset(v, 0, C * 4);
     CUtensorMap tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN;
@@ -17,7 +17,7 @@ int main() {
     bt.M = M; bt.C = C; bt.ln_eps = 1e-5f; bt.b_proj = bt.ln2_g = bt.ln2_b = bt.b_fc1 = bt.b_fc2 = bt.lnn_g = bt.lnn_b = v;
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     for (int rep = 0; rep < 3; ++rep) {
-        cudaMemset(dbg, 0, 2 * 64 * 8);
+        cudaMemset(dbg, 0, 3 * 64 * 8);
         bt.dbg = rep == 2 ? dbg : nullptr;
         cudaEventRecord(e0);
         int rc = launch_block_tail_inst<false>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, bt, 0);
@@ -26,7 +26,7 @@ int main() {
         float ms; cudaEventElapsedTime(&ms, e0, e1);
         printf("rep %d rc=%d %s %.1f us\n", rep, rc, cudaGetErrorString(e), ms * 1e3);
     }
-    static long long h[2 * 64];
+    static long long h[3 * 64];
     cudaMemcpy(h, dbg, sizeof(h), cudaMemcpyDeviceToHost);
     long long t0 = h[0];
     const char* mn[16] = {"proj0", "projEnd", "ln2ok", "fc1(0)e", "fc2(0)b", "fc2(0)e", "", "fc1(1)e", "fc2(1)b", "fc2(1)e", "", "fc1(2)e", "fc2(2)b", "fc2(2)e", "", ""};
@@ -36,7 +36,7 @@ int main() {
         for (int i = 0; i < 16; ++i) if (h[t * 16 + i]) printf(" %s=%lld", mn[i], h[t * 16 + i] - t0);
         printf("\n        EPI:");
         for (int i = 0; i < 16; ++i) if (h[64 + t * 16 + i]) printf(" %s=%lld", en[i], h[64 + t * 16 + i] - t0);
-        printf("\n");
+        printf("  reswait=%lld\n", h[128 + t]);
     }
     return 0;
 }
