@@ -123,7 +123,15 @@ __device__ __forceinline__ void tma_load_3d_pair(void* smem_dst, const CUtensorM
 }
 // Arrive on the barrier at this offset in the pair's leader CTA (works from either CTA of the pair).
 __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerBitMask) : "memory");
+// Semantics: the default (.release at CTA scope).  A cluster-scope release also has to publish this thread's prior
+// GLOBAL writes to the peer SM, i.e. a round trip to L2: measured ~750 cycles per arrive for the issuing thread
+// (scripts/probes/stream_timeline.cu), which made the epilogue the bottleneck of every pair kernel.  Nothing handed
+// over through these barriers lives in global memory: TMEM hand-backs are ordered by tcgen05.fence, shared-memory
+// operands by fence.proxy.async in the writing CTA before the arrive.
+#ifndef DDC_ARRIVE_SEM
+#define DDC_ARRIVE_SEM ""
+#endif
+    asm volatile("mbarrier.arrive" DDC_ARRIVE_SEM ".shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerBitMask) : "memory");
 }
 
 // 2-D tiled store smem -> global (bulk async group); rows / columns outside the tensor map are clipped

@@ -39,7 +39,7 @@ constexpr int G2_THREADS = 384;             // warps 0 and 3 TMA producers, warp
 constexpr int G2_EPI_WARPS = 8;             // two warps per TMEM lane quarter, alternating column chunks
 constexpr int G2_A_KB_BYTES = G2_BM * 128;
 constexpr int G2_GSLOT_BYTES = 128 * 128;   // staging unit of an epilogue group (4 warps): 128 rows x 128 B
-constexpr int G2_ES_STREAM = 1;             // staging slots per epilogue group
+constexpr int G2_ES_STREAM = 1;             // staging slots per epilogue group (a second slot costs three ring stages: measured slower)
 constexpr int G2_ES_ROW = 2;                // row-block: residual chunk in flight + chunk being processed
 constexpr int G2_TAIL_BYTES = 3072;         // barriers, TMEM slot, row-statistics exchange
 
@@ -84,6 +84,17 @@ inline size_t gemm2_smem_bytes(int K, int N, int bn, int stages, bool rowblock) 
 
 // byte offset of 16-byte chunk `j` of row `r` inside a 128-byte-swizzled 32-row slot
 __device__ __forceinline__ uint32_t slot_off(int r, int j) { return r * 128 + ((j ^ (r & 7)) << 4); }
+
+// Probes only (scripts/probes define DDC_PROBE_TIMING): per-section cycle accounting of one epilogue warp.
+#ifdef DDC_PROBE_TIMING
+#define PT_DECL long long pt_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, pt_last = clock64()
+#define PT(k) do { const long long pt_now = clock64(); pt_acc[k] += pt_now - pt_last; pt_last = pt_now; } while (0)
+#define PT_FLUSH(p) do { if ((p).dbg != nullptr && blockIdx.x == 0 && warp == 4 && lane == 0) for (int i = 0; i < 8; ++i) (p).dbg[3 * 64 + i] = pt_acc[i]; } while (0)
+#else
+#define PT_DECL
+#define PT(k)
+#define PT_FLUSH(p)
+#endif
 
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
@@ -234,7 +245,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     ++acc_it;
                 }
                 tc_fence_after();
-                if (lane == 0) g2_stamp(p, 1, (tcount * 4 + nt) * 2);
+                if (lane == 0) g2_stamp(p, 1, (tcount * 8 + nt) * 2);
                 for (int kb = 0; kb < kblocks; ++kb) {
                     if (nt == 0) mbar_wait(&afull_bar[kb], tcount & 1);
                     mbar_wait(&full_bar[stage], phase);
@@ -255,7 +266,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     __syncwarp();
                     if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
                 }
-                if (lane == 0) g2_stamp(p, 1, (tcount * 4 + nt) * 2 + 1);
+                if (lane == 0) g2_stamp(p, 1, (tcount * 8 + nt) * 2 + 1);
             }
         }
     } else if (warp >= 4) {
@@ -274,15 +285,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         const float* s_bias = smem_p;
         uint32_t tcount = 0;
         if (!ROWBLOCK) {
-            uint32_t acc_it = 0;
+            uint32_t acc_it = 0, si = 0;            // si: staging-slot counter of this group
+            PT_DECL;
             const int cpn = p.bn / 64;              // 64-column chunks per N tile (bf16 flavours)
             for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
                 const int m0 = tile * G2_BM;
                 const int row = m0 + trow;
                 for (int nt = 0; nt < num_nt; ++nt, ++acc_it) {
                     const uint32_t acc = acc_it % nacc;
+                    PT(0);
                     mbar_wait(&tfull_bar[acc], (acc_it / nacc) & 1);
                     tc_fence_after();
+                    PT(1);
+                    if (warp == 4 && lane == 0) g2_stamp(p, 2, (tcount * 8 + nt) * 2);
                     const uint32_t t_row = lane_taddr + acc * acc_stride;
                     if (EPI == S_F32) {
                         for (int c = 16 * hf; c < p.bn; c += 32) {
@@ -302,14 +317,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     } else {
                         for (int c = 0; c < cpn; ++c) {
                             if (((nt * cpn + c) & 1) != hf) continue;
-                            uint8_t* slot = grp_slots;
-                            if (gleader) bulk_wait_read<0>();      // the slot's previous store has read it
+                            uint8_t* slot = grp_slots + (si++ % ES) * G2_GSLOT_BYTES;
+                            PT(0);
+                            if (gleader) bulk_wait_read<ES - 1>();  // the slot's previous store has read it
+                            PT(2);
                             named_bar_sync(gbar, 128);
+                            PT(3);
                             const int n0 = nt * p.bn + c * 64;
 #pragma unroll
                             for (int h = 0; h < 2; ++h) {
                                 float v[32];
                                 tmem_ld32(t_row + c * 64 + 32 * h, v);
+                                PT(4);
 #pragma unroll
                                 for (int i = 0; i < 32; i += 4) {
                                     const float4 b = *reinterpret_cast<const float4*>(s_bias + n0 + 32 * h + i);
@@ -328,20 +347,25 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                                     o.w = pack2<F16>(v[8 * j + 6], v[8 * j + 7]);
                                     *reinterpret_cast<uint4*>(slot + slot_off(trow, 4 * h + j)) = o;
                                 }
+                                PT(5);
                             }
                             fence_proxy_async_smem();
                             named_bar_sync(gbar, 128);
+                            PT(6);
                             if (gleader && m0 < p.M) {
                                 tma_store_2d(&tmO, slot, n0, m0);
                                 bulk_commit();
                             }
+                            PT(7);
                         }
                     }
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) { if (CS == 1) mbar_arrive(&tempty_bar[acc]); else mbar_arrive_leader(&tempty_bar[acc]); }
+                    if (warp == 4 && lane == 0) g2_stamp(p, 2, (tcount * 8 + nt) * 2 + 1);
                 }
             }
+            PT_FLUSH(p);
         } else {
             // ---------------------------------------------------------- row-block flavour
             const int nchunk = p.N / 32;            // fp32 chunks of 128 B per row; this group takes c % 2 == hf
