@@ -141,7 +141,9 @@ static int launch_gemm2_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, con
         attr_dev_mask |= (1 << dev);
     }
     const int sms = num_sms();
-    int grid = p.num_tiles < sms ? p.num_tiles : sms;
+    // one CTA per M tile at most -- or, with the balanced unit split, per (M tile, N tile) unit
+    const long work = p.balanced ? static_cast<long>(p.num_tiles) * (p.N / p.bn) : p.num_tiles;
+    int grid = work < sms ? static_cast<int>(work) : sms;
     grid = grid / CS * CS;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
@@ -179,6 +181,7 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
     const size_t smem = gemm2_smem_bytes(p.K, p.N, p.bn / cs, p.stages, rowblock);
     if (smem > 227 * 1024) return fail(DDC_E_INVALID, "gemm: %zu B of shared memory needed", smem);
     p.num_tiles = ((p.M + G2_BM - 1) / G2_BM + cs - 1) / cs * cs;
+    p.balanced = (!rowblock && env_int("DDC_BALANCED", 1)) ? 1 : 0;
     if (f16) {
         if (cs == 2) return launch_gemm2_inst<EPI, true, 2>(tmA, tmB, tmO, tmR, tmN, p, smem, st);
         return launch_gemm2_inst<EPI, true, 1>(tmA, tmB, tmO, tmR, tmN, p, smem, st);

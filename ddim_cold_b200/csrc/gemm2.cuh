@@ -58,6 +58,7 @@ struct Gemm2Params {
     const StepEntry* tbl;
     const int* cur;
     int B;
+    int balanced;            // streaming flavours: split (M tile, N tile) units evenly over the CTA pairs
     int dbg_flags;           // probes only: 1 = no X store, 2 = no residual load, 4 = no tmem_st, 8 = skip LN passes
     long long* dbg;          // optional timeline buffer (probes only): [cta < 2][role 4][64] SM clock stamps
 };
@@ -137,6 +138,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const uint32_t crank = CS > 1 ? cluster_ctarank() : 0u;
     const int first_tile = static_cast<int>((blockIdx.x / CS) * CS + crank);
     const int tile_step = gridDim.x;
+    // Work split.  Row-block flavours need whole rows, so a CTA (pair) takes whole M tiles, strided by the grid.
+    // The streaming flavours split the (M tile, N tile) units of the whole problem into one contiguous, equally
+    // long run per CTA (pair): with 260 pair tiles on 74 pairs, whole tiles would cost four rounds where 3.5 are
+    // needed.  A run covers segments (M tile, [nt0, nt1)); a pair loads the A rows of a split tile a second time.
+    const int seg_pairs = static_cast<int>(gridDim.x) / CS, seg_pidx = static_cast<int>(blockIdx.x) / CS;
+    const long long seg_units = static_cast<long long>(p.num_tiles / CS) * num_nt;
+    const int seg_u0 = static_cast<int>(seg_units * seg_pidx / seg_pairs);
+    const int seg_u1 = static_cast<int>(seg_units * (seg_pidx + 1) / seg_pairs);
+    auto segment = [&](uint32_t k, int& tile, int& nt0, int& nt1) -> bool {
+        if (ROWBLOCK || !p.balanced) {
+            tile = first_tile + static_cast<int>(k) * tile_step;
+            nt0 = 0;
+            nt1 = num_nt;
+            return tile < p.num_tiles;
+        }
+        const int ptile = seg_u0 / num_nt + static_cast<int>(k);
+        tile = ptile * CS + static_cast<int>(crank);
+        nt0 = k == 0 ? seg_u0 % num_nt : 0;
+        nt1 = seg_u1 - ptile * num_nt < num_nt ? seg_u1 - ptile * num_nt : num_nt;
+        return nt1 > nt0;
+    };
     const bool leader = crank == 0;
     // stream flavour: as many accumulator stages as the 512 TMEM columns hold (max 4), so the MMA issuer can run
     // several N tiles ahead of the epilogue and the drain handshake stays off the critical path
@@ -187,7 +209,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (lane == 0) {
             const uint32_t me = warp == 0 ? 0u : 1u;
             uint32_t bit = 0, tcount = 0;          // bit: running index of W loads (stage = bit % stages)
-            for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
+            for (int tile, nt0, nt1; segment(tcount, tile, nt0, nt1); ++tcount) {
                 const int m0 = tile * G2_BM;
                 for (int kb = static_cast<int>(me); kb < kblocks; kb += 2) {
                     mbar_wait(&aempty_bar[kb], (tcount & 1) ^ 1);
@@ -199,9 +221,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                         tma_load_2d_pair(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0);
                     }
                 }
-                if (me == 0 && tile + tile_step < p.num_tiles)          // next tile's A rows -> L2 while this one runs
-                    for (int kb = 0; kb < kblocks; ++kb) tma_prefetch_l2_2d(&tmA, kb * G2_BK, (tile + tile_step) * G2_BM);
-                for (int nt = 0; nt < num_nt; ++nt) {
+                int ntile, na, nb;
+                if (me == 0 && segment(tcount + 1, ntile, na, nb))      // next tile's A rows -> L2 while this one runs
+                    for (int kb = 0; kb < kblocks; ++kb) tma_prefetch_l2_2d(&tmA, kb * G2_BK, ntile * G2_BM);
+                for (int nt = nt0; nt < nt1; ++nt) {
                     for (int kb = 0; kb < kblocks; ++kb, ++bit) {
                         if ((bit & 1u) != me) continue;
                         const uint32_t stage = bit % static_cast<uint32_t>(p.stages);
@@ -229,8 +252,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         const uint64_t bd0 = umma_desc_sw128(smem_u32(smem_b));
         const uint32_t b_stage_units = b_stage_bytes >> 4;
         uint32_t stage = 0, phase = 0, tcount = 0, acc_it = 0;
-        for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
-            for (int nt = 0; nt < num_nt; ++nt) {
+        for (int tile, nt0, nt1; segment(tcount, tile, nt0, nt1); ++tcount) {
+            for (int nt = nt0; nt < nt1; ++nt) {
                 uint32_t d_tmem;
                 uint64_t* done_bar;
                 if (ROWBLOCK) {
@@ -247,7 +270,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 tc_fence_after();
                 if (lane == 0) g2_stamp(p, 1, (tcount * 8 + nt) * 2);
                 for (int kb = 0; kb < kblocks; ++kb) {
-                    if (nt == 0) mbar_wait(&afull_bar[kb], tcount & 1);
+                    if (nt == nt0) mbar_wait(&afull_bar[kb], tcount & 1);
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     if (elect_one()) {
@@ -255,11 +278,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                                         bd0 + static_cast<uint64_t>(stage * b_stage_units), idesc, kb != 0 ? 1u : 0u);
                         if (CS == 1) {
                             umma_commit(&empty_bar[stage]);
-                            if (nt == num_nt - 1) umma_commit(&aempty_bar[kb]);
+                            if (nt == nt1 - 1) umma_commit(&aempty_bar[kb]);
                             if (kb == kblocks - 1) umma_commit(done_bar);
                         } else {      // both CTAs' producers / epilogues are released
                             umma_commit_pair(&empty_bar[stage]);
-                            if (nt == num_nt - 1) umma_commit_pair(&aempty_bar[kb]);
+                            if (nt == nt1 - 1) umma_commit_pair(&aempty_bar[kb]);
                             if (kb == kblocks - 1) umma_commit_pair(done_bar);
                         }
                     }
@@ -288,10 +311,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             uint32_t acc_it = 0, si = 0;            // si: staging-slot counter of this group
             PT_DECL;
             const int cpn = p.bn / 64;              // 64-column chunks per N tile (bf16 flavours)
-            for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tcount) {
+            for (int tile, nt0, nt1; segment(tcount, tile, nt0, nt1); ++tcount) {
                 const int m0 = tile * G2_BM;
                 const int row = m0 + trow;
-                for (int nt = 0; nt < num_nt; ++nt, ++acc_it) {
+                for (int nt = nt0; nt < nt1; ++nt, ++acc_it) {
                     const uint32_t acc = acc_it % nacc;
                     PT(0);
                     mbar_wait(&tfull_bar[acc], (acc_it / nacc) & 1);
