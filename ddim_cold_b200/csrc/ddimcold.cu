@@ -626,13 +626,8 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     TRY(ensure_store_maps(pl, B));
     const bool f16 = pl->f16;
     const int cs = gemm_cluster_size(M);
-    if (f16)
-        patchify_kernel<true><<<dim3(s.img_h / s.patch, B), 256, 0, st>>>(x, pl->Ap, s.img_h, s.img_w, s.patch, L,
-                                                                            pl->Kp, use_step_ctr ? pl->ctr : nullptr);
-    else
-        patchify_kernel<false><<<dim3(s.img_h / s.patch, B), 256, 0, st>>>(x, pl->Ap, s.img_h, s.img_w, s.patch, L,
-                                                                             pl->Kp, use_step_ctr ? pl->ctr : nullptr);
-    CK(cudaGetLastError());
+    CK(f16 ? launch_patchify<true>(x, pl->Ap, B, s.img_h, s.img_w, s.patch, L, pl->Kp, use_step_ctr ? pl->ctr : nullptr, st)
+           : launch_patchify<false>(x, pl->Ap, B, s.img_h, s.img_w, s.patch, L, pl->Kp, use_step_ctr ? pl->ctr : nullptr, st));
     MARK(KC_PATCHIFY);
     const LayerW& l0 = pl->layers[0];
     Gemm2Params g{};
@@ -686,9 +681,6 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     return DDC_OK;
 }
 
-static size_t head_ddim_smem(const ddc_shape& s) {
-    return static_cast<size_t>(s.img_w / s.patch) * (3 * s.patch * s.patch + 1) * sizeof(float);
-}
 
 static int check_call(ddc_plan* pl, int batch) {
     if (pl == nullptr) return fail(DDC_E_INVALID, "plan is NULL");
@@ -706,8 +698,7 @@ extern "C" int ddc_forward(ddc_plan* pl, const float* x, const int32_t* t, int32
     HeadDdimParams q{};
     q.y = pl->Y; q.ldy = pl->P; q.x = out;
     q.H = pl->sh.img_h; q.W = pl->sh.img_w; q.p = pl->sh.patch; q.L = pl->L; q.B = batch;
-    head_ddim_kernel<MODE_FORWARD><<<dim3(q.H / q.p, batch), 256, head_ddim_smem(pl->sh), st>>>(q);
-    CK(cudaGetLastError());
+    CK(launch_head_ddim<MODE_FORWARD>(q, st));
     return DDC_OK;
 }
 
@@ -816,8 +807,7 @@ extern "C" int ddc_forward_fixed_scratch(ddc_plan* pl, const float* x, const int
         HeadDdimParams q{};
         q.y = pl->Y; q.ldy = pl->P; q.x = out;
         q.H = pl->sh.img_h; q.W = pl->sh.img_w; q.p = pl->sh.patch; q.L = pl->L; q.B = batch;
-        head_ddim_kernel<MODE_FORWARD><<<dim3(q.H / q.p, batch), 256, head_ddim_smem(pl->sh), st>>>(q);
-        const cudaError_t e = cudaGetLastError();
+        const cudaError_t e = launch_head_ddim<MODE_FORWARD>(q, st);
         if (e != cudaSuccess) rc = fail(DDC_E_CUDA, "head_ddim launch: %s", cudaGetErrorString(e));
     }
     view_save(pl, &pl->fixed_view);      // keeps the store descriptors built for this batch
@@ -833,8 +823,7 @@ static int enqueue_step(ddc_plan* pl, float* x, int B, float* x0_last, float* x0
     q.H = pl->sh.img_h; q.W = pl->sh.img_w; q.p = pl->sh.patch; q.L = pl->L; q.B = B;
     q.tbl = pl->tbl; q.cur = pl->ctr;
     q.x0_last = x0_last; q.x0_seq = x0_seq; q.eps_seq = eps_seq;
-    head_ddim_kernel<MODE_STEP><<<dim3(q.H / q.p, B), 256, head_ddim_smem(pl->sh), st>>>(q);
-    CK(cudaGetLastError());
+    CK(launch_head_ddim<MODE_STEP>(q, st));
     MARK(KC_DDIM);
     return DDC_OK;
 }
@@ -1056,13 +1045,9 @@ extern "C" int ddc_k_patchify(int32_t fmt, const float* x, void* ap, int32_t bat
         Kp < 3 * patch * patch || Kp % 2)
         return fail(DDC_E_INVALID, "bad argument");
     const int L = (H / patch) * (W / patch) + 1;
-    if (fmt == 1)
-        patchify_kernel<true><<<dim3(H / patch, batch), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-            x, static_cast<bf16*>(ap), H, W, patch, L, Kp, nullptr);
-    else
-        patchify_kernel<false><<<dim3(H / patch, batch), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-            x, static_cast<bf16*>(ap), H, W, patch, L, Kp, nullptr);
-    CK(cudaGetLastError());
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    CK(fmt == 1 ? launch_patchify<true>(x, static_cast<bf16*>(ap), batch, H, W, patch, L, Kp, nullptr, st)
+                : launch_patchify<false>(x, static_cast<bf16*>(ap), batch, H, W, patch, L, Kp, nullptr, st));
     return DDC_OK;
 }
 
@@ -1076,8 +1061,6 @@ extern "C" int ddc_k_head_ddim(const float* y, int32_t ldy, float* x, int32_t ba
     memcpy(&q.one, host_step, sizeof(StepEntry));
     q.one.flags |= 1;
     q.x0_last = x0_out; q.x0_seq = nullptr; q.eps_seq = eps_out;
-    const size_t smem = static_cast<size_t>(W / patch) * (3 * patch * patch + 1) * sizeof(float);
-    head_ddim_kernel<MODE_STEP><<<dim3(H / patch, batch), 256, smem, static_cast<cudaStream_t>(stream)>>>(q);
-    CK(cudaGetLastError());
+    CK(launch_head_ddim<MODE_STEP>(q, static_cast<cudaStream_t>(stream)));
     return DDC_OK;
 }

@@ -119,6 +119,177 @@ __global__ void __launch_bounds__(256) head_ddim_kernel(const HeadDdimParams q) 
     }
 }
 
+// ---------------------------------------------------------------------------- row-group variants (vector access)
+// The two kernels above touch 4 bytes per thread per access and spend most of their instructions on index
+// arithmetic.  When W, p and ldy are multiples of 4 the variants below are used instead: a block owns R whole patch
+// rows of one image, moves the image in float4 lines (fully coalesced), and exchanges the patch-major / image-major
+// orders through shared memory, so the GEMM-side rows (Ap, Y) are read and written as contiguous 16-byte vectors
+// too.  Divisions by runtime shape values are replaced by multiply-high with host-made reciprocals.
+struct FastDiv {
+    uint32_t d, m;      // m = floor(2^32 / d) + 1; exact for n * d < 2^32 (n < 2^21, d < 2^11 here)
+};
+inline FastDiv make_fastdiv(int d) {
+    FastDiv f;
+    f.d = static_cast<uint32_t>(d);
+    f.m = d > 1 ? static_cast<uint32_t>((1ull << 32) / static_cast<uint32_t>(d)) + 1u : 0u;
+    return f;
+}
+__device__ __forceinline__ uint32_t fdiv(uint32_t n, const FastDiv f) { return f.d == 1 ? n : __umulhi(n, f.m); }
+
+struct RowGroup {
+    int R;                      // patch rows per block
+    FastDiv w4, rp, p, p4;      // W/4, R*p, p, P/4
+};
+
+// largest divisor R of Hp whose staging tile fits `budget` bytes; 0 if even one patch row does not
+inline int rows_per_block(int Hp, size_t bytes_per_patch_row, size_t budget) {
+    int best = 0;
+    for (int r = 1; r <= Hp; ++r)
+        if (Hp % r == 0 && static_cast<size_t>(r) * bytes_per_patch_row <= budget) best = r;
+    return best;
+}
+
+template <bool F16>
+__global__ void __launch_bounds__(256)
+patchify_rows_kernel(const float* __restrict__ x, bf16* __restrict__ ap, int H, int W, int p, int L, int Kp,
+                     const RowGroup rg, int* step_ctr) {
+    extern __shared__ __align__(16) uint8_t pr_tile[];      // [R*Wp][Kp] 16-bit, exactly the block's Ap rows
+    const int b = blockIdx.y, ph0 = blockIdx.x * rg.R;
+    const int Wp = W / p, pp = p * p, R = rg.R;
+    if (step_ctr != nullptr && blockIdx.x == 0 && b == 0 && threadIdx.x == 0) {
+        const int nxt = step_ctr[1];
+        step_ctr[0] = nxt;
+        step_ctr[1] = nxt + 1;
+    }
+    const int rows = R * Wp;
+    const int padw = (Kp - 3 * pp) >> 1;                     // zero K padding, in 32-bit words per row
+    for (int i = threadIdx.x; i < rows * padw; i += blockDim.x) {
+        const int r = i / padw, j = i - r * padw;
+        *reinterpret_cast<uint32_t*>(pr_tile + (static_cast<size_t>(r) * Kp + 3 * pp) * 2 + 4 * j) = 0u;
+    }
+    const uint32_t w4 = rg.w4.d;
+    const uint32_t nitems = 3u * R * p * w4;
+    const float* xb = x + static_cast<size_t>(b) * 3 * H * W;
+    for (uint32_t i = threadIdx.x; i < nitems; i += blockDim.x) {
+        const uint32_t line = fdiv(i, rg.w4), x4 = i - line * w4;
+        const uint32_t c = fdiv(line, rg.rp), yy = line - c * rg.rp.d;
+        const uint32_t r = fdiv(yy, rg.p), p1 = yy - r * p;
+        const uint32_t xx = x4 * 4, pw = fdiv(xx, rg.p), p2 = xx - pw * p;
+        const float4 v = *reinterpret_cast<const float4*>(xb + (static_cast<size_t>(c) * H + ph0 * p + yy) * W + xx);
+        uint2 o;
+        o.x = pack2<F16>(v.x, v.y);
+        o.y = pack2<F16>(v.z, v.w);
+        *reinterpret_cast<uint2*>(pr_tile + (static_cast<size_t>(r * Wp + pw) * Kp + c * pp + p1 * p + p2) * 2) = o;
+    }
+    __syncthreads();
+    uint4* dst = reinterpret_cast<uint4*>(ap + (static_cast<size_t>(b) * L + 1 + static_cast<size_t>(ph0) * Wp) * Kp);
+    const int nvec = rows * Kp / 8;
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) dst[i] = reinterpret_cast<const uint4*>(pr_tile)[i];
+    if (blockIdx.x == 0) {                                   // the cls slot's all-zero row
+        uint4* z = reinterpret_cast<uint4*>(ap + static_cast<size_t>(b) * L * Kp);
+        for (int i = threadIdx.x; i < Kp / 8; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) head_ddim_rows_kernel(const HeadDdimParams q, const RowGroup rg) {
+    extern __shared__ float ys[];
+    const int b = blockIdx.y, ph0 = blockIdx.x * rg.R;
+    const int p = q.p, W = q.W, H = q.H, R = rg.R;
+    const int Wp = W / p;
+    const int P = 3 * p * p, PS = P + 1;
+    const float* yrow = q.y + (static_cast<size_t>(b) * q.L + 1 + static_cast<size_t>(ph0) * Wp) * q.ldy;
+    const uint32_t p4 = rg.p4.d;
+    const uint32_t nld = static_cast<uint32_t>(R * Wp) * p4;
+    for (uint32_t i = threadIdx.x; i < nld; i += blockDim.x) {
+        const uint32_t row = fdiv(i, rg.p4), f4 = i - row * p4;
+        const float4 v = *reinterpret_cast<const float4*>(yrow + static_cast<size_t>(row) * q.ldy + 4 * f4);
+        float* d = ys + row * PS + 4 * f4;
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    }
+    __syncthreads();
+    StepEntry e;
+    int step = 0;
+    if (MODE == MODE_STEP) {
+        if (q.tbl != nullptr) {
+            step = *q.cur;
+            e = q.tbl[step];
+        } else {
+            e = q.one;
+        }
+    }
+    const size_t img_elems = static_cast<size_t>(3) * H * W;
+    const size_t seq_off = static_cast<size_t>(step) * q.B * img_elems;
+    const uint32_t w4 = rg.w4.d;
+    const uint32_t nitems = 3u * R * p * w4;
+    for (uint32_t i = threadIdx.x; i < nitems; i += blockDim.x) {
+        const uint32_t line = fdiv(i, rg.w4), x4 = i - line * w4;
+        const uint32_t c = fdiv(line, rg.rp), yy = line - c * rg.rp.d;
+        const uint32_t r = fdiv(yy, rg.p), p1 = yy - r * p;
+        const uint32_t xx = x4 * 4, pw = fdiv(xx, rg.p), p2 = xx - pw * p;
+        const float* src = ys + (r * Wp + pw) * PS + (p1 * p + p2) * 3 + c;
+        float4 v = make_float4(src[0], src[3], src[6], src[9]);
+        const size_t gi = (static_cast<size_t>(b) * 3 + c) * H * W + static_cast<size_t>(ph0 * p + yy) * W + xx;
+        if (MODE == MODE_FORWARD) {
+            *reinterpret_cast<float4*>(q.x + gi) = v;
+        } else {
+            v.x = fminf(fmaxf(v.x, -1.f), 1.f); v.y = fminf(fmaxf(v.y, -1.f), 1.f);
+            v.z = fminf(fmaxf(v.z, -1.f), 1.f); v.w = fminf(fmaxf(v.w, -1.f), 1.f);
+            const float4 xt = *reinterpret_cast<const float4*>(q.x + gi);
+            *reinterpret_cast<float4*>(q.x + gi) =
+                make_float4(e.a * xt.x + e.b * v.x, e.a * xt.y + e.b * v.y, e.a * xt.z + e.b * v.z, e.a * xt.w + e.b * v.w);
+            if (q.x0_seq) *reinterpret_cast<float4*>(q.x0_seq + seq_off + gi) = v;
+            if (q.eps_seq)
+                *reinterpret_cast<float4*>(q.eps_seq + seq_off + gi) =
+                    make_float4((xt.x - e.sqrt_at * v.x) * e.inv_sqrt_1mat, (xt.y - e.sqrt_at * v.y) * e.inv_sqrt_1mat,
+                                (xt.z - e.sqrt_at * v.z) * e.inv_sqrt_1mat, (xt.w - e.sqrt_at * v.w) * e.inv_sqrt_1mat);
+            if ((e.flags & 1) && q.x0_last) *reinterpret_cast<float4*>(q.x0_last + gi) = v;
+        }
+    }
+}
+
+constexpr size_t EW_TILE_BUDGET = 40 * 1024;     // staging tile per block (several blocks per SM stay resident)
+
+inline RowGroup make_rowgroup(int R, int W, int p) {
+    RowGroup rg;
+    rg.R = R;
+    rg.w4 = make_fastdiv(W / 4);
+    rg.rp = make_fastdiv(R * p);
+    rg.p = make_fastdiv(p);
+    rg.p4 = make_fastdiv(3 * p * p / 4);
+    return rg;
+}
+
+// Launchers: vector variant when the shape allows it, else the scalar kernels above.
+template <bool F16>
+inline cudaError_t launch_patchify(const float* x, bf16* ap, int B, int H, int W, int p, int L, int Kp, int* step_ctr,
+                                   cudaStream_t st) {
+    const int Hp = H / p, Wp = W / p;
+    const bool aligned = (reinterpret_cast<uintptr_t>(x) % 16 == 0) && (reinterpret_cast<uintptr_t>(ap) % 16 == 0);
+    const int R = (W % 4 == 0 && p % 4 == 0 && Kp % 8 == 0 && aligned)
+                      ? rows_per_block(Hp, static_cast<size_t>(Wp) * Kp * 2, EW_TILE_BUDGET) : 0;
+    if (R > 0)
+        patchify_rows_kernel<F16><<<dim3(Hp / R, B), 256, static_cast<size_t>(R) * Wp * Kp * 2, st>>>(
+            x, ap, H, W, p, L, Kp, make_rowgroup(R, W, p), step_ctr);
+    else
+        patchify_kernel<F16><<<dim3(Hp, B), 256, 0, st>>>(x, ap, H, W, p, L, Kp, step_ctr);
+    return cudaGetLastError();
+}
+
+template <int MODE>
+inline cudaError_t launch_head_ddim(const HeadDdimParams& q, cudaStream_t st) {
+    const int Hp = q.H / q.p, Wp = q.W / q.p;
+    const size_t row_bytes = static_cast<size_t>(Wp) * (3 * q.p * q.p + 1) * sizeof(float);
+    auto al16 = [](const void* ptr) { return reinterpret_cast<uintptr_t>(ptr) % 16 == 0; };
+    const bool aligned = al16(q.y) && al16(q.x) && al16(q.x0_last) && al16(q.x0_seq) && al16(q.eps_seq);
+    const int R = (q.W % 4 == 0 && q.p % 4 == 0 && q.ldy % 4 == 0 && aligned) ? rows_per_block(Hp, row_bytes, EW_TILE_BUDGET) : 0;
+    if (R > 0)
+        head_ddim_rows_kernel<MODE><<<dim3(Hp / R, q.B), 256, R * row_bytes, st>>>(q, make_rowgroup(R, q.W, q.p));
+    else
+        head_ddim_kernel<MODE><<<dim3(Hp, q.B), 256, row_bytes, st>>>(q);
+    return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------- weight packing (one-off)
 // fp32 [rows, cols] -> 16-bit operand format [rows, cols_pad], zero padded
 template <bool F16>
