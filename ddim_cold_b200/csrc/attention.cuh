@@ -151,7 +151,7 @@ __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], co
             }
         }
     }
-    const float i0 = 1.f / lsum[0], i1 = 1.f / lsum[2];
+    const float i0 = __frcp_rn(lsum[0]), i1 = __frcp_rn(lsum[2]);     // sums are >= 1 (the row maximum contributes 1)
 #pragma unroll
     for (int i = 0; i < DT; ++i) { o[i][0] *= i0; o[i][1] *= i0; o[i][2] *= i1; o[i][3] *= i1; }
 }
@@ -227,6 +227,113 @@ attention_group_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restri
         const int r = i >> 4, j = i & 15;
         const uint8_t* src = sm + (j >> 3) * tile_bytes + r * 128 + (((j & 7) ^ (r & 7)) << 4);
         *reinterpret_cast<uint4*>(ob + static_cast<size_t>(r) * C + j * 8) = *reinterpret_cast<const uint4*>(src);
+    }
+}
+
+// ---------------------------------------------------------------------------- persistent, double-buffered
+// Work item = (image, 64 qkv columns = 64/D heads).  A CTA walks items grid-strided and keeps TWO items' Q/K/V tiles
+// in shared memory: the TMA loads of item i+1 are in flight while the warps compute item i, so the DRAM latency that
+// a one-shot CTA pays at its start (nothing to do until its only tiles land) is hidden behind tensor-core work.  Three
+// such CTAs share an SM.  Q, K and V of an item arrive as three [lk_pad x 64] boxes in the 128-byte swizzle behind
+// one mbarrier per stage; every (head, q-tile) pair is a warp task; the output tile is staged over the Q tile and
+// leaves as 128-byte row segments.
+inline size_t att_stream_smem_bytes(int L, int KC) {
+    const int lk = (L + KC - 1) / KC * KC;
+    return 1024 + static_cast<size_t>(2 * 3) * lk * 128 + 64;
+}
+
+template <int D, int KC, bool F16>
+__global__ void __launch_bounds__(ATT_GROUP_WARPS * 32, 2)
+attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ out, int L, int C, int n_items,
+                        uint32_t n_hg_magic, float scale_log2e) {
+    extern __shared__ uint8_t att_raw[];
+    constexpr int GH = 64 / D;            // heads per item
+    constexpr int DK = D / 16, DT = D / 8;
+    const uint32_t ra = smem_u32(att_raw);
+    uint8_t* sm = att_raw + (((ra + 1023u) & ~1023u) - ra);
+    const int n_hg = C / 64;
+    const int qtiles = (L + 15) / 16;
+    const int lk_pad = (L + KC - 1) / KC * KC;      // == box rows (single key chunk: L <= KC)
+    const uint32_t tile_bytes = static_cast<uint32_t>(lk_pad) * 128u;
+    uint64_t* full = reinterpret_cast<uint64_t*>(sm + 6 * tile_bytes);     // [2] stage loaded (TMA bytes)
+    uint64_t* empty = full + 2;                                            // [2] stage released (one arrival per warp)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nwarps = blockDim.x >> 5;
+    // item -> (image, 64-column group); n_hg_magic = 2^32 / n_hg + 1 (host), exact for item * n_hg < 2^32
+    auto split = [&](int item, int& img, int& hg) {
+        img = n_hg == 1 ? item : static_cast<int>(__umulhi(static_cast<uint32_t>(item), n_hg_magic));
+        hg = item - img * n_hg;
+    };
+    auto issue = [&](int item, int s) {           // one thread: the three boxes of `item` into stage s
+        int img, hg;
+        split(item, img, hg);
+        mbar_arrive_expect_tx(&full[s], 3 * tile_bytes);
+#pragma unroll
+        for (int m = 0; m < 3; ++m)
+            tma_load_2d(sm + (s * 3 + m) * tile_bytes, &tmQKV, &full[s], m * C + hg * 64, img * L);
+    };
+    if (threadIdx.x == 0) {
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        mbar_init(&empty[0], nwarps);
+        mbar_init(&empty[1], nwarps);
+        fence_barrier_init();
+        if (static_cast<int>(blockIdx.x) < n_items) issue(blockIdx.x, 0);
+    }
+    __syncthreads();
+
+    // No CTA-wide barrier in the loop: a warp owns whole q-tiles (all GH heads of 16 query rows), stages its output
+    // over the Q rows only it reads, writes those rows out itself as 128-byte segments, then releases the stage.
+    const int g = lane >> 2, t = lane & 3;
+    int it = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+        const int s = it & 1;
+        if (threadIdx.x == 0 && item + static_cast<int>(gridDim.x) < n_items) {
+            if (it >= 1) mbar_wait(&empty[s ^ 1], ((it - 1) >> 1) & 1);    // every warp is done with item it-1
+            issue(item + gridDim.x, s ^ 1);
+        }
+        __syncwarp();
+        mbar_wait(&full[s], (it >> 1) & 1);
+        uint8_t* Qt = sm + (s * 3 + 0) * tile_bytes;
+        const uint8_t* Kt = sm + (s * 3 + 1) * tile_bytes;
+        const uint8_t* Vt = sm + (s * 3 + 2) * tile_bytes;
+        int img, hg;
+        split(item, img, hg);
+        bf16* ob = out + static_cast<size_t>(img) * L * C + hg * 64;
+        for (int qt = warp; qt < qtiles; qt += nwarps) {
+            const int q0 = qt * 16;
+#pragma unroll
+            for (int head = 0; head < GH; ++head) {
+                const int cbase = (head * D) / 8;         // first 16-byte chunk of this head in the 128-byte row
+                uint32_t qa[DK][4];
+#pragma unroll
+                for (int ks = 0; ks < DK; ++ks) {
+                    const int qrow = q0 + (lane & 7) + (((lane >> 3) & 1) << 3);
+                    ldmatrix_x4(qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], att_addr<true>(Qt, qrow, cbase + ks * 2 + (lane >> 4), 0));
+                }
+                float o[DT][4];
+                if (L > KC - 16) attend_qtile<D, KC, F16, true, 128, true>(qa, Kt, Vt, L, lk_pad, scale_log2e, lane, o, cbase);
+                else attend_qtile<D, KC, F16, true, 128, false>(qa, Kt, Vt, L, lk_pad, scale_log2e, lane, o, cbase);
+                __syncwarp();                             // all lanes have their Q fragments: reuse the patch as stage
+#pragma unroll
+                for (int dt = 0; dt < DT; ++dt) {
+                    const int r0 = q0 + g, r1 = q0 + g + 8;
+                    *reinterpret_cast<uint32_t*>(Qt + r0 * 128 + (((cbase + dt) ^ (r0 & 7)) << 4) + 4 * t) = pack2<F16>(o[dt][0], o[dt][1]);
+                    *reinterpret_cast<uint32_t*>(Qt + r1 * 128 + (((cbase + dt) ^ (r1 & 7)) << 4) + 4 * t) = pack2<F16>(o[dt][2], o[dt][3]);
+                }
+            }
+            __syncwarp();
+#pragma unroll
+            for (int i = lane; i < 16 * 8; i += 32) {     // this warp's 16 rows x 128 B
+                const int r = q0 + (i >> 3), j = i & 7;
+                if (r < L)
+                    *reinterpret_cast<uint4*>(ob + static_cast<size_t>(r) * C + j * 8) =
+                        *reinterpret_cast<const uint4*>(Qt + r * 128 + ((j ^ (r & 7)) << 4));
+            }
+        }
+        fence_proxy_async_smem();     // generic accesses to this stage are ordered before the TMA refill
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
     }
 }
 

@@ -255,6 +255,7 @@ static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads
     if (!(attr_dev_mask & (1 << dev))) {
         CK(cudaFuncSetAttribute(attention_head_kernel<D, KC, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         CK(cudaFuncSetAttribute(attention_group_kernel<D, KC, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CK(cudaFuncSetAttribute(attention_stream_kernel<D, KC, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_dev_mask |= (1 << dev);
     }
     const float scale_log2e = (1.0f / sqrtf(static_cast<float>(D))) * 1.44269504088896340736f;
@@ -262,7 +263,22 @@ static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads
     constexpr int G = 128 / D;
     const int lk_pad = (L + KC - 1) / KC * KC;
     const size_t gsmem = att_group_smem_bytes(L, KC);
-    if (heads % G == 0 && L <= KC && lk_pad <= 256 && gsmem <= 100 * 1024) {      // one image's head group per CTA
+    const size_t ssmem = att_stream_smem_bytes(L, KC);
+    if (C % 64 == 0 && L <= KC && lk_pad <= 256 && ssmem <= 75 * 1024 && !env_int("DDC_ATT_ONESHOT", 0)) {
+        // persistent CTAs, next item's tiles in flight while this one is computed
+        CUtensorMap tm;
+        TRY(make_tmap(&tm, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, lk_pad));
+        int warps = 1;
+        for (int w = 1; w <= ATT_GROUP_WARPS; ++w)
+            if (qtiles % w == 0) warps = w;                // every warp the same number of q-tiles
+        const int n_hg = C / 64;
+        const int n_items = B * n_hg;
+        const uint32_t n_hg_magic = n_hg > 1 ? static_cast<uint32_t>((1ull << 32) / static_cast<uint32_t>(n_hg)) + 1u : 0u;
+        const int per_sm = static_cast<int>((227 * 1024) / (ssmem + 1024));
+        int grid = num_sms() * (per_sm < 3 ? per_sm : 3);
+        if (grid > n_items) grid = n_items;
+        attention_stream_kernel<D, KC, F16><<<grid, warps * 32, ssmem, st>>>(tm, out, L, C, n_items, n_hg_magic, scale_log2e);
+    } else if (heads % G == 0 && L <= KC && lk_pad <= 256 && gsmem <= 100 * 1024) {      // one image's head group per CTA
         CUtensorMap tm;
         TRY(make_tmap(&tm, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, lk_pad));
         const int warps = qtiles < ATT_GROUP_WARPS ? qtiles : ATT_GROUP_WARPS;
