@@ -310,6 +310,11 @@ def main():
                 4: "block_tail_kernel (proj + LN2 + fc1 + GELU + fc2 + LN, tcgen05 cta_group::2)" if fused_tail
                    else "gemm2_kernel<R_RESID> (proj GEMM + residual + LN)"}[dom]
     whole_tf = flops_img_step * B * n_steps * args.steps * world / (dev_ms / 1e3) / 1e12 / world
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this workload
+    # (S1, 1024 images per GPU); other workloads were not captured -> null
+    ncu_traffic = {4: (250.5e6, "profiles/r01c_ncu_full.txt"), 2: (146.8e6, "profiles/r01b_ncu_full.txt")}
+    traffic, traffic_src = (ncu_traffic[dom] if (args.shape == "s1" and B == 1024 and (dom != 4 or fused_tail))
+                            else (None, None))
     line = {
         "metric": f"DDIM images/sec (N={B}/GPU, k={k})", "value": value, "unit": "images/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
@@ -329,7 +334,7 @@ def main():
         "clocks": clk,
         "roofline": {"bound": "tensor", "kernel": dom_name,
                      "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved / peak_tf,
-                     "traffic": None, "peak_source": f"{pk_src} bf16 sustained (MEASURED_PEAKS.json)",
+                     "traffic": traffic, "traffic_source": traffic_src, "peak_source": f"{pk_src} bf16 sustained (MEASURED_PEAKS.json)",
                      "flops_per_launch": dom_flops, "ms_per_launch": dom_ms,
                      "share_of_step": (cls_ms[dom] / prof_steps) / step_ms_sum},
         "kernels": kernels,

@@ -384,6 +384,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             }
             float mean, rstd;
             row_stats(shift, s1, s2, mean, rstd);
+            float nmr = -mean * rstd;              // (v - mean) * rstd * g + b  ==  fma(fma(v, rstd, nmr), g, b)
             // LayerNorm2 -> Abuf (K-major, 128-byte swizzle: 64 columns = one K block).  All proj MMAs that read
             // the O tile in Abuf completed before proj_bar[NB-1] fired.
             for (int c = hf; c < C / 64; c += 2) {
@@ -400,10 +401,10 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                         const float4 b0 = *reinterpret_cast<const float4*>(s_b2 + n0 + 8 * j);
                         const float4 b1 = *reinterpret_cast<const float4*>(s_b2 + n0 + 8 * j + 4);
                         uint4 o;
-                        o.x = pack2<F16>((v[8 * j] - mean) * rstd * g0.x + b0.x, (v[8 * j + 1] - mean) * rstd * g0.y + b0.y);
-                        o.y = pack2<F16>((v[8 * j + 2] - mean) * rstd * g0.z + b0.z, (v[8 * j + 3] - mean) * rstd * g0.w + b0.w);
-                        o.z = pack2<F16>((v[8 * j + 4] - mean) * rstd * g1.x + b1.x, (v[8 * j + 5] - mean) * rstd * g1.y + b1.y);
-                        o.w = pack2<F16>((v[8 * j + 6] - mean) * rstd * g1.z + b1.z, (v[8 * j + 7] - mean) * rstd * g1.w + b1.w);
+                        o.x = pack2<F16>(fmaf(fmaf(v[8 * j], rstd, nmr), g0.x, b0.x), fmaf(fmaf(v[8 * j + 1], rstd, nmr), g0.y, b0.y));
+                        o.y = pack2<F16>(fmaf(fmaf(v[8 * j + 2], rstd, nmr), g0.z, b0.z), fmaf(fmaf(v[8 * j + 3], rstd, nmr), g0.w, b0.w));
+                        o.z = pack2<F16>(fmaf(fmaf(v[8 * j + 4], rstd, nmr), g1.x, b1.x), fmaf(fmaf(v[8 * j + 5], rstd, nmr), g1.y, b1.y));
+                        o.w = pack2<F16>(fmaf(fmaf(v[8 * j + 6], rstd, nmr), g1.z, b1.z), fmaf(fmaf(v[8 * j + 7], rstd, nmr), g1.w, b1.w));
                         *reinterpret_cast<uint4*>(kblk + slot_off(trow, 4 * h + j)) = o;
                     }
                 }
@@ -497,6 +498,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             }
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 10);
             row_stats(shift, s1, s2, mean, rstd);
+            nmr = -mean * rstd;
             for (int c = hf; c < C / 64; c += 2, ++ri) {
                 uint8_t* slot = gslots + (ri & 1u) * G2_GSLOT_BYTES;
                 if (gleader) bulk_wait_read<1>();
@@ -515,10 +517,10 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                         const float4 b0 = *reinterpret_cast<const float4*>(s_bn + n0 + 8 * j);
                         const float4 b1 = *reinterpret_cast<const float4*>(s_bn + n0 + 8 * j + 4);
                         uint4 o;
-                        o.x = pack2<F16>((v[8 * j] + a0.x - mean) * rstd * g0.x + b0.x, (v[8 * j + 1] + a0.y - mean) * rstd * g0.y + b0.y);
-                        o.y = pack2<F16>((v[8 * j + 2] + a0.z - mean) * rstd * g0.z + b0.z, (v[8 * j + 3] + a0.w - mean) * rstd * g0.w + b0.w);
-                        o.z = pack2<F16>((v[8 * j + 4] + a1.x - mean) * rstd * g1.x + b1.x, (v[8 * j + 5] + a1.y - mean) * rstd * g1.y + b1.y);
-                        o.w = pack2<F16>((v[8 * j + 6] + a1.z - mean) * rstd * g1.z + b1.z, (v[8 * j + 7] + a1.w - mean) * rstd * g1.w + b1.w);
+                        o.x = pack2<F16>(fmaf(fmaf(v[8 * j] + a0.x, rstd, nmr), g0.x, b0.x), fmaf(fmaf(v[8 * j + 1] + a0.y, rstd, nmr), g0.y, b0.y));
+                        o.y = pack2<F16>(fmaf(fmaf(v[8 * j + 2] + a0.z, rstd, nmr), g0.z, b0.z), fmaf(fmaf(v[8 * j + 3] + a0.w, rstd, nmr), g0.w, b0.w));
+                        o.z = pack2<F16>(fmaf(fmaf(v[8 * j + 4] + a1.x, rstd, nmr), g1.x, b1.x), fmaf(fmaf(v[8 * j + 5] + a1.y, rstd, nmr), g1.y, b1.y));
+                        o.w = pack2<F16>(fmaf(fmaf(v[8 * j + 6] + a1.z, rstd, nmr), g1.z, b1.z), fmaf(fmaf(v[8 * j + 7] + a1.w, rstd, nmr), g1.w, b1.w));
                         *reinterpret_cast<uint4*>(slot + slot_off(trow, 4 * h + j)) = o;
                     }
                 }
