@@ -170,6 +170,8 @@ __global__ void __launch_bounds__(ATT_GROUP_WARPS * 32, 2)
 attention_group_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ out, int L, int C,
                        float scale_log2e) {
     extern __shared__ uint8_t att_raw[];
+    pdl_launch_dependents();
+    pdl_wait();        // qkv comes from the previous kernel; nothing worth doing before it
     constexpr int G = 128 / D;            // heads per CTA
     constexpr int DK = D / 16, DT = D / 8;
     const uint32_t ra = smem_u32(att_raw);
@@ -247,6 +249,8 @@ __global__ void __launch_bounds__(ATT_GROUP_WARPS * 32, 2)
 attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ out, int L, int C, int n_items,
                         uint32_t n_hg_magic, float scale_log2e) {
     extern __shared__ uint8_t att_raw[];
+    pdl_launch_dependents();
+    pdl_wait();        // qkv comes from the previous kernel; nothing worth doing before it
     constexpr int GH = 64 / D;            // heads per item
     constexpr int DK = D / 16, DT = D / 8;
     const uint32_t ra = smem_u32(att_raw);
@@ -347,6 +351,8 @@ template <int D, int KC, bool F16>
 __global__ void __launch_bounds__(ATT_MAX_WARPS * 32)
 attention_head_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int L, int C, float scale_log2e) {
     extern __shared__ __align__(16) uint8_t att_smem[];
+    pdl_launch_dependents();
+    pdl_wait();        // qkv comes from the previous kernel; nothing worth doing before it
     constexpr int RS = (D + 8) * 2;
     constexpr int DT = D / 8, DK = D / 16;
     const int head = blockIdx.x;

@@ -67,6 +67,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                   const __grid_constant__ CUtensorMap tmXN,     // XN     [M, C]    16 bit, box 64 x 128 (store)
                   const BlockTailParams p) {
     extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
 
@@ -140,6 +141,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();        // set-up above touched only weights; O and X come from earlier kernels
     // Phase stagger.  Every pair walks the same phases per tile -- HBM reads (O, residual), an MLP stretch that moves no
     // activation bytes, HBM writes (X, XN) -- and with all pairs in lockstep the memory system sees bursts it cannot
     // absorb followed by idle time.  When the tile count does not divide evenly, the pairs that run one round fewer

@@ -8,6 +8,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
+#include <utility>
 
 namespace ddc {
 
@@ -368,6 +370,56 @@ __device__ __forceinline__ float gelu_erf(float x) {
     float e;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(hx * hx * -2.88539008178f));   // exp(-x^2/2) = 2^(-(x/2)^2 * 4 * log2(e)/2)
     return fmaf(-(ha * poly), e, hx + ha);
+}
+
+
+// ---------------------------------------------------------------------------- programmatic dependent launch
+// The 25 kernels of a denoise step form a strict chain.  Launched plainly, each one starts only after its predecessor
+// has fully drained, and then spends its first microseconds on set-up (barrier init, TMEM allocation, descriptor
+// prefetch, parameters into shared memory) with the GPU otherwise idle.  With the programmatic-serialization launch
+// attribute a kernel's CTAs are scheduled as soon as SMs free up in the predecessor's tail; they run their set-up and
+// then block in pdl_wait() until the predecessor has completed and its writes are visible.  Rules kept by every
+// step-path kernel: (1) pdl_launch_dependents() first thing; (2) nothing produced on the step path is read, and
+// nothing at all is written to global memory, before pdl_wait(); (3) EVERY kernel calls pdl_wait(), so completion
+// is transitive along the chain (a kernel that passed its wait knows all earlier kernels are done).
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("DDC_PDL");       // tuning aid: DDC_PDL=0 launches every kernel fully serialised
+        v = (e != nullptr && atoi(e) == 0) ? 0 : 1;
+    }
+    return v != 0;
+}
+
+// cudaLaunchKernelEx with an optional cluster dimension and the programmatic-serialization attribute
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chain(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster,
+                                Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    unsigned n = 0;
+    if (cluster > 1) {
+        attr[n].id = cudaLaunchAttributeClusterDimension;
+        attr[n].val.clusterDim.x = static_cast<unsigned>(cluster);
+        attr[n].val.clusterDim.y = 1;
+        attr[n].val.clusterDim.z = 1;
+        ++n;
+    }
+    if (pdl_enabled()) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = n;
+    return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
 }
 
 }  // namespace ddc

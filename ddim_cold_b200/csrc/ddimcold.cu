@@ -145,19 +145,7 @@ static int launch_gemm2_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, con
     const long work = p.balanced ? static_cast<long>(p.num_tiles) * (p.N / p.bn) : p.num_tiles;
     int grid = work < sms ? static_cast<int>(work) : sms;
     grid = grid / CS * CS;
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(G2_THREADS);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CS;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    CK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmO, tmR, tmN, p));
+    CK(launch_chain(kern, dim3(grid), dim3(G2_THREADS), smem, st, CS, tmA, tmB, tmO, tmR, tmN, p));
     return DDC_OK;
 }
 
@@ -220,19 +208,8 @@ static int launch_block_tail_inst(const CUtensorMap& tmO, const CUtensorMap& tmW
     const int sms = num_sms();
     int grid = p.num_tiles < sms ? p.num_tiles : sms;
     grid = grid / 2 * 2;
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(BT_THREADS);
-    cfg.dynamicSmemBytes = block_tail_smem_bytes(p.C, stages, p.gk);
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    CK(cudaLaunchKernelEx(&cfg, kern, tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, p));
+    CK(launch_chain(kern, dim3(grid), dim3(BT_THREADS), block_tail_smem_bytes(p.C, stages, p.gk), st, 2, tmO, tmWp, tmW1, tmW2,
+                    tmXld, tmXst, tmXN, p));
     return DDC_OK;
 }
 
@@ -277,17 +254,20 @@ static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads
         const int per_sm = static_cast<int>((227 * 1024) / (ssmem + 1024));
         int grid = num_sms() * (per_sm < 3 ? per_sm : 3);
         if (grid > n_items) grid = n_items;
-        attention_stream_kernel<D, KC, F16><<<grid, warps * 32, ssmem, st>>>(tm, out, L, C, n_items, n_hg_magic, scale_log2e);
+        CK(launch_chain(attention_stream_kernel<D, KC, F16>, dim3(grid), dim3(warps * 32), ssmem, st, 1, tm, out, L, C, n_items,
+                        n_hg_magic, scale_log2e));
     } else if (heads % G == 0 && L <= KC && lk_pad <= 256 && gsmem <= 100 * 1024) {      // one image's head group per CTA
         CUtensorMap tm;
         TRY(make_tmap(&tm, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, lk_pad));
         const int warps = qtiles < ATT_GROUP_WARPS ? qtiles : ATT_GROUP_WARPS;
-        attention_group_kernel<D, KC, F16><<<dim3(heads / G, B), warps * 32, gsmem, st>>>(tm, out, L, C, scale_log2e);
+        CK(launch_chain(attention_group_kernel<D, KC, F16>, dim3(heads / G, B), dim3(warps * 32), gsmem, st, 1, tm, out, L, C,
+                        scale_log2e));
     } else {
         const size_t smem = att_head_smem_bytes(L, D, KC);
         if (smem > 227 * 1024) return fail(DDC_E_INVALID, "attention: L=%d needs %zu B of shared memory", L, smem);
         const int warps = qtiles < ATT_MAX_WARPS ? qtiles : ATT_MAX_WARPS;
-        attention_head_kernel<D, KC, F16><<<dim3(heads, B), warps * 32, smem, st>>>(qkv, out, L, C, scale_log2e);
+        CK(launch_chain(attention_head_kernel<D, KC, F16>, dim3(heads, B), dim3(warps * 32), smem, st, 1, qkv, out, L, C,
+                        scale_log2e));
     }
     CK(cudaGetLastError());
     return DDC_OK;

@@ -17,6 +17,8 @@ template <bool F16>
 __global__ void __launch_bounds__(256)
 patchify_kernel(const float* __restrict__ x, bf16* __restrict__ ap, int H, int W, int p, int L, int Kp,
                 int* step_ctr) {
+    pdl_launch_dependents();
+    pdl_wait();                 // reads x, writes Ap and the step counter: all after the previous kernel
     const int ph = blockIdx.x, b = blockIdx.y;
     const int Wp = W / p;
     const int pp = p * p;
@@ -76,6 +78,8 @@ struct HeadDdimParams {
 template <int MODE>
 __global__ void __launch_bounds__(256) head_ddim_kernel(const HeadDdimParams q) {
     extern __shared__ float ys[];
+    pdl_launch_dependents();
+    pdl_wait();
     const int ph = blockIdx.x, b = blockIdx.y;
     const int p = q.p, W = q.W, H = q.H;
     const int Wp = W / p;
@@ -154,6 +158,8 @@ __global__ void __launch_bounds__(256)
 patchify_rows_kernel(const float* __restrict__ x, bf16* __restrict__ ap, int H, int W, int p, int L, int Kp,
                      const RowGroup rg, int* step_ctr) {
     extern __shared__ __align__(16) uint8_t pr_tile[];      // [R*Wp][Kp] 16-bit, exactly the block's Ap rows
+    pdl_launch_dependents();
+    pdl_wait();                 // reads x, writes Ap and the step counter: all after the previous kernel
     const int b = blockIdx.y, ph0 = blockIdx.x * rg.R;
     const int Wp = W / p, pp = p * p, R = rg.R;
     if (step_ctr != nullptr && blockIdx.x == 0 && b == 0 && threadIdx.x == 0) {
@@ -194,6 +200,8 @@ patchify_rows_kernel(const float* __restrict__ x, bf16* __restrict__ ap, int H, 
 template <int MODE>
 __global__ void __launch_bounds__(256) head_ddim_rows_kernel(const HeadDdimParams q, const RowGroup rg) {
     extern __shared__ float ys[];
+    pdl_launch_dependents();
+    pdl_wait();
     const int b = blockIdx.y, ph0 = blockIdx.x * rg.R;
     const int p = q.p, W = q.W, H = q.H, R = rg.R;
     const int Wp = W / p;
@@ -269,11 +277,9 @@ inline cudaError_t launch_patchify(const float* x, bf16* ap, int B, int H, int W
     const int R = (W % 4 == 0 && p % 4 == 0 && Kp % 8 == 0 && aligned)
                       ? rows_per_block(Hp, static_cast<size_t>(Wp) * Kp * 2, EW_TILE_BUDGET) : 0;
     if (R > 0)
-        patchify_rows_kernel<F16><<<dim3(Hp / R, B), 256, static_cast<size_t>(R) * Wp * Kp * 2, st>>>(
-            x, ap, H, W, p, L, Kp, make_rowgroup(R, W, p), step_ctr);
-    else
-        patchify_kernel<F16><<<dim3(Hp, B), 256, 0, st>>>(x, ap, H, W, p, L, Kp, step_ctr);
-    return cudaGetLastError();
+        return launch_chain(patchify_rows_kernel<F16>, dim3(Hp / R, B), dim3(256), static_cast<size_t>(R) * Wp * Kp * 2, st, 1,
+                            x, ap, H, W, p, L, Kp, make_rowgroup(R, W, p), step_ctr);
+    return launch_chain(patchify_kernel<F16>, dim3(Hp, B), dim3(256), 0, st, 1, x, ap, H, W, p, L, Kp, step_ctr);
 }
 
 template <int MODE>
@@ -284,10 +290,9 @@ inline cudaError_t launch_head_ddim(const HeadDdimParams& q, cudaStream_t st) {
     const bool aligned = al16(q.y) && al16(q.x) && al16(q.x0_last) && al16(q.x0_seq) && al16(q.eps_seq);
     const int R = (q.W % 4 == 0 && q.p % 4 == 0 && q.ldy % 4 == 0 && aligned) ? rows_per_block(Hp, row_bytes, EW_TILE_BUDGET) : 0;
     if (R > 0)
-        head_ddim_rows_kernel<MODE><<<dim3(Hp / R, q.B), 256, R * row_bytes, st>>>(q, make_rowgroup(R, q.W, q.p));
-    else
-        head_ddim_kernel<MODE><<<dim3(Hp, q.B), 256, row_bytes, st>>>(q);
-    return cudaGetLastError();
+        return launch_chain(head_ddim_rows_kernel<MODE>, dim3(Hp / R, q.B), dim3(256), R * row_bytes, st, 1, q,
+                            make_rowgroup(R, q.W, q.p));
+    return launch_chain(head_ddim_kernel<MODE>, dim3(Hp, q.B), dim3(256), row_bytes, st, 1, q);
 }
 
 // ---------------------------------------------------------------------------- weight packing (one-off)

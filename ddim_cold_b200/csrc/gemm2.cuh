@@ -109,6 +109,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     constexpr bool ROWBLOCK = (EPI == R_RESID || EPI == R_EMBED);
     constexpr int ES = ROWBLOCK ? G2_ES_ROW : G2_ES_STREAM;
     extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();
     const uint32_t raw_addr = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
 
@@ -201,6 +202,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     if (CS > 1) cluster_sync_all();              // peers' barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();        // set-up above touched only weights; activations and the step counter come from earlier kernels
 
     if (warp == 0 || warp == 3) {
         // ================================================================= TMA producers
