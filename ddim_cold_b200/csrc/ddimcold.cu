@@ -318,6 +318,7 @@ struct ddc_plan {
     float *lnf_g, *lnf_b, *b_head;
     bf16* w_head;
     CUtensorMap tm_wpatch[2], tm_whead[2];
+    CUtensorMap tm_posb;                     // position table [L + 127, C] fp32, box 32 x 128 (the embed GEMM's "residual")
     // work arena
     float* X;
     bf16 *QKV, *O, *Hd, *Ap, *XN;
@@ -380,7 +381,7 @@ static void carve(ddc_plan* pl, void* weight_arena, void* work_arena, size_t* wb
     const size_t C = pl->C, L = pl->L, P = pl->P, Kp = pl->Kp, Mp = pl->Mpad;
     Carver w{static_cast<char*>(weight_arena), 0};
     pl->w_patch = w.take<bf16>(C * Kp);
-    pl->posb = w.take<float>(L * C);
+    pl->posb = w.take<float>((L + 127) * C);        // position rows, extended so any tile's 128 rows are contiguous
     pl->time_tab = w.take<float>(static_cast<size_t>(s.total_steps) * C);
     pl->layers.resize(s.depth);
     for (auto& l : pl->layers) {
@@ -475,6 +476,7 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
     mk(&pl->tm_Hd, false, pl->Hd, Mp, C, G2_BM);
     mk(&pl->tm_XN, false, pl->XN, Mp, C, G2_BM);
     mk(&pl->tm_Xld, true, pl->X, Mp, C, G2_BM);
+    mk(&pl->tm_posb, true, pl->posb, static_cast<uint64_t>(pl->L) + 127, C, G2_BM);
     for (int cs = 1; cs <= 2; ++cs) {
         mk(&pl->tm_wpatch[cs - 1], false, pl->w_patch, C, pl->Kp, pl->bn_row / cs);
         mk(&pl->tm_whead[cs - 1], false, pl->w_head, pl->P, C, pl->bn_head / cs);
@@ -541,7 +543,7 @@ extern "C" int ddc_pack_weights(ddc_plan* pl, const float* const* t, int32_t n_t
     const float* cls = t[0];
     const float* pos = t[1];
     pack(t[2], pl->w_patch, C, P, pl->Kp);
-    pack_posb_kernel<<<148, 256, 0, st>>>(pos, cls, t[3], pl->posb, L, C);
+    pack_posb_kernel<<<148, 256, 0, st>>>(pos, cls, t[3], pl->posb, L, C, L + 127);
     copy(t[4], pl->time_tab, static_cast<size_t>(pl->sh.total_steps) * C);
     for (int i = 0; i < pl->sh.depth; ++i) {
         const float* const* b = t + 5 + 12 * i;
@@ -630,7 +632,7 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     g.M = M; g.N = C; g.K = pl->Kp; g.bn = pl->bn_row; g.stages = pick_stages2(g.K, g.N, g.bn / cs, true);
     g.ln_g = l0.ln1_g; g.ln_b = l0.ln1_b; g.ln_eps = 1e-5f;
     g.posb = pl->posb; g.L = L; g.time_tab = pl->time_tab; g.t_img = t_img; g.tbl = pl->tbl; g.cur = pl->ctr; g.B = B;
-    TRY((launch_gemm2<R_EMBED>(pl->tm_Ap, pl->tm_wpatch[cs - 1], pl->st_X, pl->tm_Xld, pl->st_XN, g, f16, cs, st)));
+    TRY((launch_gemm2<R_EMBED>(pl->tm_Ap, pl->tm_wpatch[cs - 1], pl->st_X, pl->tm_posb, pl->st_XN, g, f16, cs, st)));
     MARK(KC_EMBED);
     for (int i = 0; i < s.depth; ++i) {
         LayerW& l = pl->layers[i];

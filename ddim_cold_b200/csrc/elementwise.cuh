@@ -309,13 +309,16 @@ __global__ void pack_16bit_kernel(const float* __restrict__ src, bf16* __restric
     }
 }
 
-// posb[0] = cls + pos[0];  posb[l>0] = pos[l] + conv_bias   (ViT.py:150,202-205)
+// posb[0] = cls + pos[0];  posb[l>0] = pos[l] + conv_bias   (ViT.py:150,202-205), written for `rows` >= L table rows
+// with row i holding position i % L: token rows m0 .. m0+127 of any 128-row GEMM tile are then the contiguous table
+// rows (m0 % L) .. (m0 % L) + 127, one TMA box.
 __global__ void pack_posb_kernel(const float* __restrict__ pos, const float* __restrict__ cls,
-                                 const float* __restrict__ conv_bias, float* __restrict__ posb, int L, int C) {
-    const int n = L * C;
+                                 const float* __restrict__ conv_bias, float* __restrict__ posb, int L, int C, int rows) {
+    const int n = rows * C;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const int l = i / C, c = i - l * C;
-        posb[i] = pos[i] + (l == 0 ? cls[c] : conv_bias[c]);
+        const int r = i / C, c = i - r * C;
+        const int l = r % L;
+        posb[i] = pos[l * C + c] + (l == 0 ? cls[c] : conv_bias[c]);
     }
 }
 

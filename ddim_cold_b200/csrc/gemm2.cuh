@@ -20,7 +20,8 @@
 //      S_F32        out = acc + bias  (fp32, direct stores)       head  (ViT.py:213)
 //  * row-block (R_*): N == embed_dim, the whole 128 x C fp32 row block lives in TMEM.
 //      pass 1  v = acc + bias + X   (R_RESID, X prefetched by TMA; ViT.py:136-137)
-//              v = acc + posb[l] + time[t]  (R_EMBED; ViT.py:154,202-205)
+//              v = acc + posb[l] + time[t]  (R_EMBED; ViT.py:154,202-205: posb rows come by TMA from a table
+//                                            extended to L + 127 rows so a tile's 128 rows are contiguous in it)
 //              v -> X (fp32, TMA store), v -> back into TMEM, row sum
 //      pass 2  exact two-pass variance from TMEM
 //      pass 3  XN = bf16(LayerNorm(v) * g + b) -> TMA store.  XN is the *next* GEMM's A
@@ -51,7 +52,7 @@ struct Gemm2Params {
     const float* ln_g;       // R_*: parameters of the LayerNorm that FOLLOWS this GEMM
     const float* ln_b;
     float ln_eps;
-    const float* posb;       // R_EMBED
+    const float* posb;       // R_EMBED: [L + 127, N] with row i = position row i % L (only read through tmR)
     int L;
     const float* time_tab;
     const int* t_img;
@@ -171,7 +172,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         if (EPI != S_F32) tma_prefetch_desc(&tmO);
-        if (EPI == R_RESID) tma_prefetch_desc(&tmR);
+        if (ROWBLOCK) tma_prefetch_desc(&tmR);
         if (ROWBLOCK) tma_prefetch_desc(&tmN);
         for (int i = 0; i < 8; ++i) {
             mbar_init(&full_bar[i], 1);
@@ -190,7 +191,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     }
     if (warp >= 4) {
         for (int i = threadIdx.x - 128; i < p.N; i += G2_EPI_WARPS * 32) {
-            if (EPI != R_EMBED) smem_p[i] = p.bias[i];
+            if (EPI != R_EMBED) smem_p[i] = p.bias[i];      // R_EMBED: the time row, staged after pdl_wait below
             if (ROWBLOCK) {
                 smem_p[p.N + i] = p.ln_g[i];
                 smem_p[2 * p.N + i] = p.ln_b[i];
@@ -203,6 +204,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();        // set-up above touched only weights; activations and the step counter come from earlier kernels
+    if (EPI == R_EMBED && warp >= 4) {
+        // "bias" of the patch GEMM = the timestep embedding row (ViT.py:205).  In the sampling loop every image shares
+        // t (read from the device step table); forward() with per-image t adds the rows per thread instead.
+        const float* trow = p.t_img == nullptr ? p.time_tab + static_cast<size_t>(p.tbl[*p.cur].t) * p.N : nullptr;
+        for (int i = threadIdx.x - 128; i < p.N; i += G2_EPI_WARPS * 32) smem_p[i] = trow != nullptr ? trow[i] : 0.f;
+        named_bar_sync(7, G2_EPI_WARPS * 32);
+    }
 
     if (warp == 0 || warp == 3) {
         // ================================================================= TMA producers
@@ -414,21 +422,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 const int row = m0 + trow;
                 if (EPI == R_RESID && gleader && tile + tile_step < p.num_tiles)
                     for (int c = hf; c < nchunk; c += 2) tma_prefetch_l2_2d(&tmR, c * 32, (tile + tile_step) * G2_BM);
-                const float* embed_pos = nullptr;
-                const float* embed_time = nullptr;
-                if (EPI == R_EMBED) {
+                const float* embed_time = nullptr;      // per-image t only (forward())
+                if (EPI == R_EMBED && p.t_img != nullptr) {
                     int b = row / p.L;
-                    const int l = row - b * p.L;
                     if (b > p.B - 1) b = p.B - 1;
-                    const int t = p.t_img ? p.t_img[b] : p.tbl[*p.cur].t;
-                    embed_pos = p.posb + static_cast<size_t>(l) * p.N;
-                    embed_time = p.time_tab + static_cast<size_t>(t) * p.N;
+                    embed_time = p.time_tab + static_cast<size_t>(p.t_img[b]) * p.N;
                 }
-                if (EPI == R_RESID && hf < nchunk && gleader && !(p.dbg_flags & 2)) {
+                // residual rows: X[m0 ..] (R_RESID) or the position rows of these tokens, (m0 % L) + r in the table
+                const int r_row = EPI == R_EMBED ? m0 % p.L : m0;
+                if (hf < nchunk && gleader && !(p.dbg_flags & 2)) {
                     bulk_wait_read<0>();            // slots may still feed the previous tile's XN stores
                     const uint32_t s = ri % ES;
                     mbar_arrive_expect_tx(&my_res[s], G2_GSLOT_BYTES);
-                    tma_load_2d(grp_slots + s * G2_GSLOT_BYTES, &tmR, &my_res[s], hf * 32, m0);
+                    tma_load_2d(grp_slots + s * G2_GSLOT_BYTES, &tmR, &my_res[s], hf * 32, r_row);
                 }
                 if (warp == 4 && lane == 0) g2_stamp(p, 2, tcount * 4);
                 float sum = 0.f;
@@ -438,13 +444,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     uint8_t* slot = grp_slots + s * G2_GSLOT_BYTES;
                     if (gleader) {
                         bulk_wait_read<0>();        // the other slot's store (previous chunk) has released it
-                        if (EPI == R_RESID && c + 2 < nchunk && !(p.dbg_flags & 2)) {
+                        if (c + 2 < nchunk && !(p.dbg_flags & 2)) {
                             const uint32_t s2 = (ri + 1) % ES;
                             mbar_arrive_expect_tx(&my_res[s2], G2_GSLOT_BYTES);
-                            tma_load_2d(grp_slots + s2 * G2_GSLOT_BYTES, &tmR, &my_res[s2], (c + 2) * 32, m0);
+                            tma_load_2d(grp_slots + s2 * G2_GSLOT_BYTES, &tmR, &my_res[s2], (c + 2) * 32, r_row);
                         }
                     }
-                    if (EPI == R_EMBED) named_bar_sync(gbar, 128);     // slot free for every warp of the group
                     const int n0 = c * 32;
                     const int nt = n0 / p.bn;
                     if (nt != waited_nt) {
@@ -454,25 +459,22 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     }
                     float v[32];
                     tmem_ld32(lane_taddr + n0, v);
-                    if (EPI == R_RESID) {
-                        if (!(p.dbg_flags & 2)) {
-                            mbar_wait(&my_res[s], (res_phase >> s) & 1);
-                            res_phase ^= (1u << s);
-                        }
+                    if (!(p.dbg_flags & 2)) {
+                        mbar_wait(&my_res[s], (res_phase >> s) & 1);
+                        res_phase ^= (1u << s);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 r = *reinterpret_cast<const float4*>(slot + slot_off(trow, j));
+                        const float4 b = *reinterpret_cast<const float4*>(s_bias + n0 + 4 * j);
+                        v[4 * j] += r.x + b.x; v[4 * j + 1] += r.y + b.y;
+                        v[4 * j + 2] += r.z + b.z; v[4 * j + 3] += r.w + b.w;
+                    }
+                    if (EPI == R_EMBED && embed_time != nullptr) {
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
-                            const float4 r = *reinterpret_cast<const float4*>(slot + slot_off(trow, j));
-                            const float4 b = *reinterpret_cast<const float4*>(s_bias + n0 + 4 * j);
-                            v[4 * j] += r.x + b.x; v[4 * j + 1] += r.y + b.y;
-                            v[4 * j + 2] += r.z + b.z; v[4 * j + 3] += r.w + b.w;
-                        }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 a = __ldg(reinterpret_cast<const float4*>(embed_pos + n0 + 4 * j));
                             const float4 b = __ldg(reinterpret_cast<const float4*>(embed_time + n0 + 4 * j));
-                            v[4 * j] += a.x + b.x; v[4 * j + 1] += a.y + b.y;
-                            v[4 * j + 2] += a.z + b.z; v[4 * j + 3] += a.w + b.w;
+                            v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
                         }
                     }
 #pragma unroll
