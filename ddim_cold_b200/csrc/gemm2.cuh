@@ -22,9 +22,8 @@
 //      pass 1  v = acc + bias + X   (R_RESID, X prefetched by TMA; ViT.py:136-137)
 //              v = acc + posb[l] + time[t]  (R_EMBED; ViT.py:154,202-205: posb rows come by TMA from a table
 //                                            extended to L + 127 rows so a tile's 128 rows are contiguous in it)
-//              v -> X (fp32, TMA store), v -> back into TMEM, row sum
-//      pass 2  exact two-pass variance from TMEM
-//      pass 3  XN = bf16(LayerNorm(v) * g + b) -> TMA store.  XN is the *next* GEMM's A
+//              v -> X (fp32, TMA store), v -> back into TMEM, shifted row sums (one-pass statistics)
+//      pass 2  XN = bf16(LayerNorm(v) * g + b) -> TMA store.  XN is the *next* GEMM's A
 //              operand, so LayerNorm (ViT.py:133,137,212) never costs its own pass over HBM.
 #pragma once
 
@@ -437,7 +436,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     tma_load_2d(grp_slots + s * G2_GSLOT_BYTES, &tmR, &my_res[s], hf * 32, r_row);
                 }
                 if (warp == 4 && lane == 0) g2_stamp(p, 2, tcount * 4);
-                float sum = 0.f;
+                // one-pass statistics: sums around a shift (the row's first value in this group's columns, so nothing
+                // cancels), merged exactly with the partner group's half (same scheme as block_tail.cuh)
+                float shift = 0.f, s1 = 0.f, s2 = 0.f;
                 int waited_nt = -1;
                 for (int c = hf; c < nchunk; c += 2, ++ri) {
                     const uint32_t s = ri % ES;
@@ -477,8 +478,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                             v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
                         }
                     }
+                    if (c == hf) shift = v[0];
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) sum += v[i];
+                    for (int i = 0; i < 32; ++i) {
+                        const float d = v[i] - shift;
+                        s1 += d;
+                        s2 = fmaf(d, d, s2);
+                    }
                     if (!(p.dbg_flags & 4)) tmem_st32(lane_taddr + n0, v);
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
@@ -491,26 +497,23 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                         bulk_commit();
                     }
                 }
-                // ---- row statistics: exact two-pass variance; the two column halves exchange partials
+                // ---- row statistics: each group turns its sums into (mean, M2) of its half of the row; halves of equal
+                // count n/2 merge as mean = (m0 + m1)/2, M2 = M2_0 + M2_1 + n/4 (m0 - m1)^2  (Chan et al.)
                 if (warp == 4 && lane == 0) g2_stamp(p, 2, tcount * 4 + 1);
-                *red_sum = sum;
+                const float half_n = 0.5f * static_cast<float>(p.N);
+                const float mg = shift + s1 / half_n;
+                const float m2g = s2 - s1 * s1 / half_n;
+                *red_sum = mg;
+                *red_sq = m2g;
                 tc_fence_before();                  // the partner's pass 3 reads TMEM columns this warp stored
                 named_bar_sync(3 + q, 64);
                 tc_fence_after();
-                const float mean = (sum + *oth_sum) * inv_n;
-                float sq = 0.f;
-                for (int c = hf; c < nchunk; c += 2) {
-                    float v[32];
-                    tmem_ld32(lane_taddr + c * 32, v);
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        const float d = v[i] - mean;
-                        sq += d * d;
-                    }
-                }
-                *red_sq = sq;
-                named_bar_sync(3 + q, 64);
-                const float rstd = rsqrtf((sq + *oth_sq) * inv_n + p.ln_eps);
+                const float mo = *oth_sum, m2o = *oth_sq;
+                const float mean = 0.5f * (mg + mo);
+                const float dm = mg - mo;
+                const float rstd = rsqrtf((m2g + m2o + 0.5f * half_n * dm * dm) * inv_n + p.ln_eps);
+                const float nmr = -mean * rstd;
+                named_bar_sync(3 + q, 64);          // both partners have read the exchange slots before they are reused
                 if (warp == 4 && lane == 0) g2_stamp(p, 2, tcount * 4 + 2);
                 for (int c = hf; c < ((p.dbg_flags & 8) ? 0 : p.N / 64); c += 2, ++ri) {
                     uint8_t* slot = grp_slots + (ri % ES) * G2_GSLOT_BYTES;
@@ -528,10 +531,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                             const float4 b0 = *reinterpret_cast<const float4*>(s_beta + n0 + 8 * j);
                             const float4 b1 = *reinterpret_cast<const float4*>(s_beta + n0 + 8 * j + 4);
                             uint4 o;
-                            o.x = pack2<F16>((v[8 * j] - mean) * rstd * g0.x + b0.x, (v[8 * j + 1] - mean) * rstd * g0.y + b0.y);
-                            o.y = pack2<F16>((v[8 * j + 2] - mean) * rstd * g0.z + b0.z, (v[8 * j + 3] - mean) * rstd * g0.w + b0.w);
-                            o.z = pack2<F16>((v[8 * j + 4] - mean) * rstd * g1.x + b1.x, (v[8 * j + 5] - mean) * rstd * g1.y + b1.y);
-                            o.w = pack2<F16>((v[8 * j + 6] - mean) * rstd * g1.z + b1.z, (v[8 * j + 7] - mean) * rstd * g1.w + b1.w);
+                            o.x = pack2<F16>(fmaf(fmaf(v[8 * j], rstd, nmr), g0.x, b0.x), fmaf(fmaf(v[8 * j + 1], rstd, nmr), g0.y, b0.y));
+                            o.y = pack2<F16>(fmaf(fmaf(v[8 * j + 2], rstd, nmr), g0.z, b0.z), fmaf(fmaf(v[8 * j + 3], rstd, nmr), g0.w, b0.w));
+                            o.z = pack2<F16>(fmaf(fmaf(v[8 * j + 4], rstd, nmr), g1.x, b1.x), fmaf(fmaf(v[8 * j + 5], rstd, nmr), g1.y, b1.y));
+                            o.w = pack2<F16>(fmaf(fmaf(v[8 * j + 6], rstd, nmr), g1.z, b1.z), fmaf(fmaf(v[8 * j + 7], rstd, nmr), g1.w, b1.w));
                             *reinterpret_cast<uint4*>(slot + slot_off(trow, 4 * h + j)) = o;
                         }
                     }
