@@ -329,7 +329,7 @@ struct ddc_plan {
     CUtensorMap tm_Xld;                      // residual loads (fp32, box 32 x 32, padded row count)
     // store maps are clipped to exactly batch*L rows, so they are rebuilt when the batch changes
     int maps_B;
-    CUtensorMap st_QKV, st_Hd, st_XN, st_X;
+    CUtensorMap st_QKV, st_Hd, st_XN, st_X, st_Y;      // st_Y only when P % 32 == 0 (fp32 boxes are 32 columns wide)
     // graph cache
     cudaGraphExec_t gexec;
     GraphKey gkey;
@@ -341,7 +341,7 @@ struct ddc_plan {
         float* Y;
         StepEntry* tbl;
         int* ctr;
-        CUtensorMap tm_Ap, tm_O, tm_Hd, tm_XN, tm_Xld, st_QKV, st_Hd, st_XN, st_X;
+        CUtensorMap tm_Ap, tm_O, tm_Hd, tm_XN, tm_Xld, st_QKV, st_Hd, st_XN, st_X, st_Y;
         int maps_B, Mpad, maxB;
         cudaGraphExec_t gexec;
     };
@@ -606,6 +606,7 @@ static int ensure_store_maps(ddc_plan* pl, int B) {
     TRY(make_tmap(&pl->st_Hd, false, pl->Hd, M, C, G2_BM));
     TRY(make_tmap(&pl->st_XN, false, pl->XN, M, C, G2_BM));
     TRY(make_tmap(&pl->st_X, true, pl->X, M, C, G2_BM));
+    if (pl->P % 32 == 0) TRY(make_tmap(&pl->st_Y, true, pl->Y, M, pl->P, G2_BM));
     pl->maps_B = B;
     if (pl->gexec) {                 // the captured graph holds the old maps by value
         cudaGraphExecDestroy(pl->gexec);
@@ -674,7 +675,8 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     Gemm2Params h{};
     h.M = M; h.N = pl->P; h.K = C; h.bn = pl->bn_head; h.stages = pick_stages2(h.K, h.N, h.bn / cs, false);
     h.bias = pl->b_head; h.out_f32 = pl->Y; h.ld_f32 = pl->P;
-    TRY((launch_gemm2<S_F32>(pl->tm_XN, pl->tm_whead[cs - 1], pl->st_XN, pl->tm_Xld, pl->st_XN, h, f16, cs, st)));
+    h.f32_tma = (pl->P % 32 == 0 && h.bn % 32 == 0) ? 1 : 0;      // TMA-staged fp32 stores when the boxes fit
+    TRY((launch_gemm2<S_F32>(pl->tm_XN, pl->tm_whead[cs - 1], h.f32_tma ? pl->st_Y : pl->st_XN, pl->tm_Xld, pl->st_XN, h, f16, cs, st)));
     MARK(KC_HEAD);
     return DDC_OK;
 }
@@ -738,7 +740,7 @@ static void view_save(const ddc_plan* pl, ddc_plan::WorkView* v) {
     v->X = pl->X; v->QKV = pl->QKV; v->O = pl->O; v->Hd = pl->Hd; v->Ap = pl->Ap; v->XN = pl->XN; v->Y = pl->Y;
     v->tbl = pl->tbl; v->ctr = pl->ctr;
     v->tm_Ap = pl->tm_Ap; v->tm_O = pl->tm_O; v->tm_Hd = pl->tm_Hd; v->tm_XN = pl->tm_XN; v->tm_Xld = pl->tm_Xld;
-    v->st_QKV = pl->st_QKV; v->st_Hd = pl->st_Hd; v->st_XN = pl->st_XN; v->st_X = pl->st_X;
+    v->st_QKV = pl->st_QKV; v->st_Hd = pl->st_Hd; v->st_XN = pl->st_XN; v->st_X = pl->st_X; v->st_Y = pl->st_Y;
     v->maps_B = pl->maps_B; v->Mpad = pl->Mpad; v->maxB = pl->maxB; v->gexec = pl->gexec;
 }
 
@@ -746,7 +748,7 @@ static void view_install(ddc_plan* pl, const ddc_plan::WorkView* v) {
     pl->X = v->X; pl->QKV = v->QKV; pl->O = v->O; pl->Hd = v->Hd; pl->Ap = v->Ap; pl->XN = v->XN; pl->Y = v->Y;
     pl->tbl = v->tbl; pl->ctr = v->ctr;
     pl->tm_Ap = v->tm_Ap; pl->tm_O = v->tm_O; pl->tm_Hd = v->tm_Hd; pl->tm_XN = v->tm_XN; pl->tm_Xld = v->tm_Xld;
-    pl->st_QKV = v->st_QKV; pl->st_Hd = v->st_Hd; pl->st_XN = v->st_XN; pl->st_X = v->st_X;
+    pl->st_QKV = v->st_QKV; pl->st_Hd = v->st_Hd; pl->st_XN = v->st_XN; pl->st_X = v->st_X; pl->st_Y = v->st_Y;
     pl->maps_B = v->maps_B; pl->Mpad = v->Mpad; pl->maxB = v->maxB; pl->gexec = v->gexec;
 }
 
@@ -978,6 +980,11 @@ extern "C" int ddc_k_gemm(int32_t fmt, int32_t epi, int32_t M, int32_t N, int32_
             return launch_gemm2<S_BF16_GELU>(tmA, tmB, tmO, tmA, tmA, p, f16, cs, st);
         case S_F32:
             p.out_f32 = static_cast<float*>(out); p.ld_f32 = ld_out;
+            if (N % 32 == 0 && bn % 32 == 0) {
+                p.f32_tma = 1;
+                TRY(make_tmap(&tmO, true, out, M, N, G2_BM));
+                return launch_gemm2<S_F32>(tmA, tmB, tmO, tmA, tmA, p, f16, cs, st);
+            }
             return launch_gemm2<S_F32>(tmA, tmB, tmA, tmA, tmA, p, f16, cs, st);
     }
     return fail(DDC_E_INVALID, "epi=%d", epi);

@@ -48,6 +48,7 @@ struct Gemm2Params {
     const float* bias;
     float* out_f32;          // S_F32
     int ld_f32;
+    int f32_tma;             // S_F32: stage 32-column chunks and store them by TMA (tmO = fp32 map) instead of per-row stores
     const float* ln_g;       // R_*: parameters of the LayerNorm that FOLLOWS this GEMM
     const float* ln_b;
     float ln_eps;
@@ -170,7 +171,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
-        if (EPI != S_F32) tma_prefetch_desc(&tmO);
+        if (EPI != S_F32 || p.f32_tma) tma_prefetch_desc(&tmO);
         if (ROWBLOCK) tma_prefetch_desc(&tmR);
         if (ROWBLOCK) tma_prefetch_desc(&tmN);
         for (int i = 0; i < 8; ++i) {
@@ -331,7 +332,31 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                     PT(1);
                     if (warp == 4 && lane == 0) g2_stamp(p, 2, (tcount * 8 + nt) * 2);
                     const uint32_t t_row = lane_taddr + acc * acc_stride;
-                    if (EPI == S_F32) {
+                    if (EPI == S_F32 && p.f32_tma) {
+                        // fp32 output in 32-column chunks: [128 rows x 128 B] slot per group, one TMA store each
+                        const int cpn32 = p.bn / 32;
+                        for (int c = 0; c < cpn32; ++c) {
+                            if (((nt * cpn32 + c) & 1) != hf) continue;
+                            uint8_t* slot = grp_slots + (si++ % ES) * G2_GSLOT_BYTES;
+                            if (gleader) bulk_wait_read<ES - 1>();
+                            named_bar_sync(gbar, 128);
+                            const int n0 = nt * p.bn + c * 32;
+                            float v[32];
+                            tmem_ld32(t_row + c * 32, v);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                const float4 b = *reinterpret_cast<const float4*>(s_bias + n0 + 4 * j);
+                                *reinterpret_cast<float4*>(slot + slot_off(trow, j)) =
+                                    make_float4(v[4 * j] + b.x, v[4 * j + 1] + b.y, v[4 * j + 2] + b.z, v[4 * j + 3] + b.w);
+                            }
+                            fence_proxy_async_smem();
+                            named_bar_sync(gbar, 128);
+                            if (gleader && m0 < p.M) {
+                                tma_store_2d(&tmO, slot, n0, m0);
+                                bulk_commit();
+                            }
+                        }
+                    } else if (EPI == S_F32) {
                         for (int c = 16 * hf; c < p.bn; c += 32) {
                             float v[16];
                             tmem_ld16(t_row + c, v);
