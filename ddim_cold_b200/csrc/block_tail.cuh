@@ -27,7 +27,12 @@
 
 namespace ddc {
 
-constexpr int BT_THREADS = 384;              // warps 0,3 TMA, warp1 MMA (pair leader), warp2 TMEM, warps 4-11 epilogue
+// warps 0,3 TMA, warp 1 MMA (pair leader), warp 2 TMEM, then NG epilogue groups of four warps.  NG = 2 (384 threads) is
+// the default.  NG = 4 (640 threads) exists as a measured alternative: 640 threads start at 96 registers each and
+// setmaxnreg can only move registers inside what the CTA got at launch (640 x 96 = 61440; asking for more blocks
+// forever), so the four control warps shrink to 64 and the epilogue warps grow to 104.  It is slower (see the launcher).
+__host__ __device__ constexpr int bt_threads(int ng) { return 128 + 128 * ng; }
+constexpr int BT_TAIL_BYTES = 6144;          // barriers, TMEM slot, row-statistics exchange [2][4][128], residual barriers
 constexpr int BT_BN = 128;                   // N tile of every GEMM in here
 constexpr int BT_HSLOT_BYTES = 2 * G2_A_KB_BYTES;   // one hidden block: 128 rows x 128 cols, two K blocks
 
@@ -47,17 +52,21 @@ struct BlockTailParams {
     int stagger;             // SM cycles by which CTA pairs with a spare round start late (0 = off), see the kernel
 };
 
+// Timeline stamps exist only in probe builds (scripts/probes define DDC_PROBE_TIMING): in the product kernel they would
+// cost registers the 16-warp epilogue does not have.
 __device__ __forceinline__ void bt_stamp(const BlockTailParams& p, int role, int idx) {
+#ifdef DDC_PROBE_TIMING
     if (p.dbg != nullptr && blockIdx.x == 0 && idx < 64) p.dbg[role * 64 + idx] = clock64();
+#endif
 }
 
 inline size_t block_tail_smem_bytes(int C, int stages, int gk) {
     return 1024 + static_cast<size_t>(C / 64) * G2_A_KB_BYTES + 2 * BT_HSLOT_BYTES + static_cast<size_t>(stages) * gk * 64 * 128 +
-           ((static_cast<size_t>(7) * C * 4 + 127) & ~static_cast<size_t>(127)) + G2_TAIL_BYTES;
+           ((static_cast<size_t>(7) * C * 4 + 127) & ~static_cast<size_t>(127)) + BT_TAIL_BYTES;
 }
 
-template <bool F16>
-__global__ void __launch_bounds__(BT_THREADS, 1)
+template <bool F16, int NG>
+__global__ void __launch_bounds__(bt_threads(NG), 1)
 block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad, C] 16 bit, box 64 x 128 (A operand)
                   const __grid_constant__ CUtensorMap tmWp,     // Wproj  [C, C]    16 bit, box 64 x 64
                   const __grid_constant__ CUtensorMap tmW1,     // Wfc1
@@ -95,9 +104,9 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     uint64_t* hfree_bar = bars + 34;      // [2]  hidden block consumed by fc2  (pair commit)
     uint64_t* final_bar = bars + 36;      // [1]  row block holds X1 + H Wfc2^T (pair commit)
     uint64_t* tfree_bar = bars + 42;      // [4]  N tile of the row block drained by epi3 (leader, 16 arrivals)
-    uint64_t* res_bar = bars + 38;        // [4]  residual chunk landed (group x slot)
+    uint64_t* res_bar = bars + 576;       // [4]  residual chunk landed (group x slot), behind the statistics area
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 48);
-    float* red = reinterpret_cast<float*>(bars + 64);     // [2 stats][2 groups][128 rows]
+    float* red = reinterpret_cast<float*>(bars + 64);     // [2 stats][NG groups][128 rows]
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -118,9 +127,9 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         for (int i = 0; i < 4; ++i) mbar_init(&proj_bar[i], 1);
         for (int i = 0; i < 8; ++i) mbar_init(&ln2_bar[i], 8);
         mbar_init(t1full_bar, 1);
-        mbar_init(t1free_bar, 16);
-        mbar_init(&hready_bar[0], 16);
-        mbar_init(&hready_bar[1], 16);
+        mbar_init(t1free_bar, 8 * NG);              // every epilogue warp of both CTAs
+        mbar_init(&hready_bar[0], 8 * NG);
+        mbar_init(&hready_bar[1], 8 * NG);
         mbar_init(&hfree_bar[0], 1);
         mbar_init(&hfree_bar[1], 1);
         mbar_init(final_bar, 1);
@@ -134,7 +143,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     }
     if (warp >= 4) {
         const float* src[7] = {p.b_proj, p.ln2_g, p.ln2_b, p.b_fc1, p.b_fc2, p.lnn_g, p.lnn_b};
-        for (int i = threadIdx.x - 128; i < 7 * C; i += 256) sp[i] = src[i / C][i % C];
+        for (int i = threadIdx.x - 128; i < 7 * C; i += 128 * NG) sp[i] = src[i / C][i % C];
     }
     tc_fence_before();
     __syncthreads();
@@ -154,6 +163,10 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             const long long t0 = clock64();
             while (clock64() - t0 < p.stagger) __nanosleep(256);
         }
+    }
+    if (NG == 4) {     // warp-group aligned: warps 0-3 shrink, the sixteen epilogue warps grow (see bt_threads)
+        if (warp < 4) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
     }
     const float* s_bproj = sp;
     const float* s_g2 = sp + C;
@@ -288,64 +301,74 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             }
         }
     } else if (warp >= 4) {
-        // ================================================================= epilogue (8 warps, two groups of four)
+        // ================================================================= epilogue (NG groups of four warps)
+        // Warp (q, hf): TMEM lane quarter q (rows 32q .. 32q+31 of the tile, thread = row), column group hf.  Groups take
+        // 32-column chunks (fp32 passes) or 64-column chunks (16-bit passes) round-robin.  Hbuf doubles as staging:
+        // SL = 4 / NG slots of 16 KB per group.
+        constexpr int SL = 4 / NG;
         const int q = warp & 3;
         const int hf = (warp - 4) >> 2;
         const bool gleader = q == 0 && lane == 0;
-        const int gbar = 1 + hf;
+        const int gbar = 1 + hf;                      // named barrier of the group (128 threads), ids 1 .. NG
+        const int pbar = 8 + q;                       // named barrier of the NG warps that share lane quarter q
         const int trow = q * 32 + lane;
         const uint32_t lane_taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-        uint8_t* gslots = hbuf + static_cast<size_t>(hf) * BT_HSLOT_BYTES;     // two 16 KB staging slots per group
-        uint64_t* my_res = res_bar + hf * 2;
+        uint8_t* gslots = hbuf + static_cast<size_t>(hf) * SL * G2_GSLOT_BYTES;
+        uint64_t* my_res = res_bar + hf * SL;
         const int nchunk = C / 32;
+        const int nper = (nchunk - hf + NG - 1) / NG;          // 32-column chunks of this group
         const float inv_c = 1.0f / static_cast<float>(C);
-        float* red_sum = red + hf * 128 + trow;
-        float* red_sq = red + 256 + hf * 128 + trow;
-        const float* oth_sum = red + (hf ^ 1) * 128 + trow;
-        const float* oth_sq = red + 256 + (hf ^ 1) * 128 + trow;
+        float* red_mean = red + hf * 128 + trow;                // [2 stats][NG groups][128 rows]
+        float* red_m2 = red + NG * 128 + hf * 128 + trow;
         uint32_t tc = 0, g = 0, ri = 0, res_phase = 0;
 
-        // LayerNorm statistics in one pass over the data: each group accumulates sum and sum of squares of its half of
+        // LayerNorm statistics in one pass over the data: each group accumulates sum and sum of squares of its part of
         // the row around a shift K (the first value it sees, so nothing cancels), turns them into (mean, M2) of that
-        // half, and the halves are merged with the exact pairwise update (Chan et al.): equal counts n = C/2,
-        // mean = (m0 + m1)/2, M2 = M2_0 + M2_1 + n/2 (m0 - m1)^2.
-        const float half_n = 0.5f * static_cast<float>(C);
+        // part, and the NG equal-sized parts are merged exactly (Chan et al.): mean = avg(m_i),
+        // M2 = sum(M2_i) + n_part * sum((m_i - mean)^2).
+        const float part_n = static_cast<float>(C) / static_cast<float>(NG);
         auto row_stats = [&](float shift, float s1, float s2, float& mean, float& rstd) {
-            const float mg = shift + s1 / half_n;
-            const float m2g = s2 - s1 * s1 / half_n;
-            *red_sum = mg;
-            *red_sq = m2g;
-            tc_fence_before();                  // the partner group later reads TMEM columns this warp stored
-            named_bar_sync(3 + q, 64);
+            const float mg = shift + s1 / part_n;
+            const float m2g = s2 - s1 * s1 / part_n;
+            *red_mean = mg;
+            *red_m2 = m2g;
+            tc_fence_before();                  // the partner groups later read TMEM columns this warp stored
+            named_bar_sync(pbar, 32 * NG);
             tc_fence_after();
-            const float mo = *oth_sum, m2o = *oth_sq;
-            mean = 0.5f * (mg + mo);
-            const float d = mg - mo;
-            const float m2 = m2g + m2o + 0.5f * half_n * d * d;
+            float ms[NG], msum = 0.f, m2 = 0.f;
+#pragma unroll
+            for (int i = 0; i < NG; ++i) {
+                ms[i] = red[i * 128 + trow];
+                msum += ms[i];
+                m2 += red[NG * 128 + i * 128 + trow];
+            }
+            mean = msum * (1.0f / NG);
+#pragma unroll
+            for (int i = 0; i < NG; ++i) m2 = fmaf(part_n * (ms[i] - mean), ms[i] - mean, m2);
             rstd = rsqrtf(m2 * inv_c + p.ln_eps);
-            named_bar_sync(3 + q, 64);          // both partners have read the exchange slots before they are reused
+            named_bar_sync(pbar, 32 * NG);      // every partner has read the exchange slots before they are reused
         };
 
-        if (gleader && first_tile < p.num_tiles)
-            for (int c = hf; c < nchunk; c += 2) tma_prefetch_l2_2d(&tmXld, c * 32, first_tile * G2_BM);
         for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++tc) {
             const int m0 = tile * G2_BM;
 
             // ------------------------------------------------------------ epi1: X1 = acc + b_proj + X -> TMEM
             if (gleader) {
                 bulk_wait_read<0>();               // the previous tile's X / XN stores have read the staging slots
-                for (int i = 0; i < 2 && hf + 2 * i < nchunk; ++i) {      // both slots in flight from the start
-                    const uint32_t s = (ri + i) & 1u;
-                    mbar_arrive_expect_tx(&my_res[s], G2_GSLOT_BYTES);
-                    tma_load_2d(gslots + s * G2_GSLOT_BYTES, &tmXld, &my_res[s], (hf + 2 * i) * 32, m0);
+                for (int k = 0; k < SL && k < nper; ++k) {               // all of the group's slots in flight
+                    mbar_arrive_expect_tx(&my_res[k], G2_GSLOT_BYTES);
+                    tma_load_2d(gslots + k * G2_GSLOT_BYTES, &tmXld, &my_res[k], (hf + NG * k) * 32, m0);
                 }
             }
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 0);
             float shift = 0.f, s1 = 0.f, s2 = 0.f;
             int waited = -1;
+#ifdef DDC_PROBE_TIMING
             long long res_wait = 0;                // probes only: cycles this warp waited for residual chunks
-            for (int c = hf; c < nchunk; c += 2, ++ri) {
-                const uint32_t s = ri & 1u;
+#endif
+            for (int k = 0; k < nper; ++k) {
+                const int c = hf + NG * k;
+                const uint32_t s = static_cast<uint32_t>(k % SL);
                 uint8_t* slot = gslots + s * G2_GSLOT_BYTES;
                 const int n0 = c * 32;
                 if (n0 / BT_BN != waited) {
@@ -355,9 +378,13 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 }
                 float v[32];
                 tmem_ld32(lane_taddr + n0, v);
+#ifdef DDC_PROBE_TIMING
                 const long long w0 = (p.dbg != nullptr) ? clock64() : 0;
+#endif
                 mbar_wait(&my_res[s], (res_phase >> s) & 1);
+#ifdef DDC_PROBE_TIMING
                 if (p.dbg != nullptr) res_wait += clock64() - w0;
+#endif
                 res_phase ^= (1u << s);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
@@ -366,7 +393,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     v[4 * j] += r.x + b.x; v[4 * j + 1] += r.y + b.y;
                     v[4 * j + 2] += r.z + b.z; v[4 * j + 3] += r.w + b.w;
                 }
-                if (c == hf) shift = v[0];
+                if (k == 0) shift = v[0];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
                     const float d = v[i] - shift;
@@ -374,22 +401,26 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     s2 = fmaf(d, d, s2);
                 }
                 tmem_st32(lane_taddr + n0, v);
-                named_bar_sync(gbar, 128);         // every warp of the group has read the slot before it is refilled
-                if (gleader && c + 4 < nchunk) {   // two loads per group stay in flight: each has two iterations to land
-                    mbar_arrive_expect_tx(&my_res[s], G2_GSLOT_BYTES);
-                    tma_load_2d(slot, &tmXld, &my_res[s], (c + 4) * 32, m0);
+                if (k + SL < nper) {
+                    named_bar_sync(gbar, 128);     // every warp of the group has read the slot before it is refilled
+                    if (gleader) {
+                        mbar_arrive_expect_tx(&my_res[s], G2_GSLOT_BYTES);
+                        tma_load_2d(slot, &tmXld, &my_res[s], (c + NG * SL) * 32, m0);
+                    }
                 }
             }
             if (warp == 4 && lane == 0) {
                 bt_stamp(p, 1, tc * 16 + 1);
+#ifdef DDC_PROBE_TIMING
                 if (p.dbg != nullptr && blockIdx.x == 0 && tc < 4) p.dbg[128 + tc] = res_wait;
+#endif
             }
             float mean, rstd;
             row_stats(shift, s1, s2, mean, rstd);
             float nmr = -mean * rstd;              // (v - mean) * rstd * g + b  ==  fma(fma(v, rstd, nmr), g, b)
             // LayerNorm2 -> Abuf (K-major, 128-byte swizzle: 64 columns = one K block).  All proj MMAs that read
             // the O tile in Abuf completed before proj_bar[NB-1] fired.
-            for (int c = hf; c < C / 64; c += 2) {
+            for (int c = hf; c < C / 64; c += NG) {
                 uint8_t* kblk = abuf + static_cast<size_t>(c) * G2_A_KB_BYTES;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
@@ -417,31 +448,29 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             }
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 2);
 
-            // the MLP phase moves no activation bytes: the quiet window for the next tile's residual rows -> L2
-            if (gleader && tile + tile_step < p.num_tiles && (p.flags & 1))
-                for (int c = hf; c < nchunk; c += 2) tma_prefetch_l2_2d(&tmXld, c * 32, (tile + tile_step) * G2_BM);
-
             // ------------------------------------------------------------ epi2(j): H_j = gelu(acc + b_fc1) -> Hbuf
+            constexpr int HW = BT_BN / NG;         // hidden columns of a block per group: 64 (two groups) or 32 (four)
             for (int j = 0; j < NB; ++j, ++g) {
                 const uint32_t hs = g & 1u;
                 mbar_wait(t1full_bar, g & 1u);
                 tc_fence_after();
                 if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 3 + 2 * j);
                 if (g >= 2) mbar_wait(&hfree_bar[hs], ((g >> 1) & 1u) ^ 1u);   // fc2 partial(g-2) has read this slot
-                // group hf converts hidden columns [64*hf, +64) of the block = K block hf of the slot
-                uint8_t* kblk = hbuf + static_cast<size_t>(hs) * BT_HSLOT_BYTES + static_cast<size_t>(hf) * G2_A_KB_BYTES;
-                // read this thread's 64 accumulator columns, then hand the accumulator back at once: fc1 of the next
+                // read this thread's accumulator columns, then hand the accumulator back at once: fc1 of the next
                 // hidden block overlaps the GELU below
-                float vv[2][32];
-                tmem_ld32(lane_taddr + static_cast<uint32_t>(C) + hf * 64, vv[0]);
-                tmem_ld32(lane_taddr + static_cast<uint32_t>(C) + hf * 64 + 32, vv[1]);
+                float vv[HW / 32][32];
+#pragma unroll
+                for (int h = 0; h < HW / 32; ++h)
+                    tmem_ld32(lane_taddr + static_cast<uint32_t>(C) + hf * HW + 32 * h, vv[h]);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive_leader(t1free_bar);
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
+                for (int h = 0; h < HW / 32; ++h) {
                     float (&v)[32] = vv[h];
-                    const int c0 = hf * 64 + 32 * h;
+                    const int c0 = hf * HW + 32 * h;                  // column inside the hidden block
+                    uint8_t* kblk = hbuf + static_cast<size_t>(hs) * BT_HSLOT_BYTES + static_cast<size_t>(c0 >> 6) * G2_A_KB_BYTES;
+                    const int jb = (c0 & 63) >> 3;                    // first 16-byte chunk inside the 128-byte row
 #pragma unroll
                     for (int i = 0; i < 32; i += 4) {
                         const float4 b = *reinterpret_cast<const float4*>(s_bfc1 + j * BT_BN + c0 + i);
@@ -455,7 +484,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                         o.y = pack2<F16>(v[8 * jj + 2], v[8 * jj + 3]);
                         o.z = pack2<F16>(v[8 * jj + 4], v[8 * jj + 5]);
                         o.w = pack2<F16>(v[8 * jj + 6], v[8 * jj + 7]);
-                        *reinterpret_cast<uint4*>(kblk + slot_off(trow, 4 * h + jj)) = o;
+                        *reinterpret_cast<uint4*>(kblk + slot_off(trow, jb + jj)) = o;
                     }
                 }
                 fence_proxy_async_smem();
@@ -464,16 +493,18 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 if (lane == 0) mbar_arrive_leader(&hready_bar[hs]);
                 if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 4 + 2 * j);
             }
+            // the MLP phase moves no activation bytes: (measured) an L2 prefetch of the next tile's residual here is no gain
+            if (gleader && tile + tile_step < p.num_tiles && (p.flags & 1))
+                for (int c = hf; c < nchunk; c += NG) tma_prefetch_l2_2d(&tmXld, c * 32, (tile + tile_step) * G2_BM);
 
             // ------------------------------------------------------------ epi3: X' = TMEM + b_fc2 -> X, LN_next -> XN
             mbar_wait(final_bar, tc & 1);
             tc_fence_after();
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 9);
             s1 = 0.f; s2 = 0.f;
-            for (int c = hf; c < nchunk; c += 2, ++ri) {
-                uint8_t* slot = gslots + (ri & 1u) * G2_GSLOT_BYTES;
-                if (gleader) bulk_wait_read<1>();
-                named_bar_sync(gbar, 128);
+            for (int k = 0; k < nper; ++k, ++ri) {
+                const int c = hf + NG * k;
+                uint8_t* slot = gslots + (ri % SL) * G2_GSLOT_BYTES;
                 const int n0 = c * 32;
                 float v[32];
                 tmem_ld32(lane_taddr + n0, v);
@@ -481,16 +512,20 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 for (int j = 0; j < 8; ++j) {
                     const float4 b = *reinterpret_cast<const float4*>(s_bfc2 + n0 + 4 * j);
                     v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
-                    *reinterpret_cast<float4*>(slot + slot_off(trow, j)) =
-                        make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                 }
-                if (c == hf) shift = v[0];
+                if (k == 0) shift = v[0];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
                     const float d = v[i] - shift;
                     s1 += d;
                     s2 = fmaf(d, d, s2);
                 }
+                if (gleader) bulk_wait_read<SL - 1>();   // the store that last used this slot has read it
+                named_bar_sync(gbar, 128);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<float4*>(slot + slot_off(trow, j)) =
+                        make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                 fence_proxy_async_smem();
                 named_bar_sync(gbar, 128);
                 if (gleader && m0 < p.M) {
@@ -501,9 +536,9 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 10);
             row_stats(shift, s1, s2, mean, rstd);
             nmr = -mean * rstd;
-            for (int c = hf; c < C / 64; c += 2, ++ri) {
-                uint8_t* slot = gslots + (ri & 1u) * G2_GSLOT_BYTES;
-                if (gleader) bulk_wait_read<1>();
+            for (int c = hf; c < C / 64; c += NG, ++ri) {
+                uint8_t* slot = gslots + (ri % SL) * G2_GSLOT_BYTES;
+                if (gleader) bulk_wait_read<SL - 1>();   // the store that last used this slot has read it
                 named_bar_sync(gbar, 128);
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
@@ -526,7 +561,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                         *reinterpret_cast<uint4*>(slot + slot_off(trow, 4 * h + j)) = o;
                     }
                 }
-                // groups 0 / 1 hold the two 64-column halves of N tile c / 2: once both are read out, the next tile's
+                // the two 64-column halves of N tile c / 2 belong to two groups: once both are read out, the next tile's
                 // proj may overwrite those TMEM columns while the remaining N tiles are still being normalised
                 tc_fence_before();
                 __syncwarp();

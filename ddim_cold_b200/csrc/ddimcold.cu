@@ -183,14 +183,14 @@ static bool block_tail_usable(int M, int C, int bn_row) {
     return C % 128 == 0 && C <= 384 && bn_row == 128 && (M + G2_BM - 1) / G2_BM >= 2 && !env_int("DDC_NO_FUSE", 0);
 }
 
-template <bool F16>
-static int launch_block_tail_inst(const CUtensorMap& tmO, const CUtensorMap& tmWp, const CUtensorMap& tmW1,
+template <bool F16, int NG>
+static int launch_block_tail_ng(const CUtensorMap& tmO, const CUtensorMap& tmWp, const CUtensorMap& tmW1,
                                   const CUtensorMap& tmW2, const CUtensorMap& tmXld, const CUtensorMap& tmXst,
                                   const CUtensorMap& tmXN, BlockTailParams p, cudaStream_t st) {
     static int attr_dev_mask = 0;
     int dev = 0;
     CK(cudaGetDevice(&dev));
-    auto kern = block_tail_kernel<F16>;
+    auto kern = block_tail_kernel<F16, NG>;
     if (!(attr_dev_mask & (1 << dev))) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_dev_mask |= (1 << dev);
@@ -208,9 +208,20 @@ static int launch_block_tail_inst(const CUtensorMap& tmO, const CUtensorMap& tmW
     const int sms = num_sms();
     int grid = p.num_tiles < sms ? p.num_tiles : sms;
     grid = grid / 2 * 2;
-    CK(launch_chain(kern, dim3(grid), dim3(BT_THREADS), block_tail_smem_bytes(p.C, stages, p.gk), st, 2, tmO, tmWp, tmW1, tmW2,
+    CK(launch_chain(kern, dim3(grid), dim3(bt_threads(NG)), block_tail_smem_bytes(p.C, stages, p.gk), st, 2, tmO, tmWp, tmW1, tmW2,
                     tmXld, tmXst, tmXN, p));
     return DDC_OK;
+}
+
+template <bool F16>
+static int launch_block_tail_inst(const CUtensorMap& tmO, const CUtensorMap& tmWp, const CUtensorMap& tmW1,
+                                  const CUtensorMap& tmW2, const CUtensorMap& tmXld, const CUtensorMap& tmXst,
+                                  const CUtensorMap& tmXN, BlockTailParams p, cudaStream_t st) {
+    // Sixteen epilogue warps (DDC_TAIL_GROUPS=4) measured SLOWER than eight (129 vs 117 us): the passes are paced by
+    // TMEM read bandwidth (64 B/clk/SM, five 196 KB passes per tile) and per-chunk hand-shakes, not by warp count.
+    if (env_int("DDC_TAIL_GROUPS", 2) == 4)
+        return launch_block_tail_ng<F16, 4>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, p, st);
+    return launch_block_tail_ng<F16, 2>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, p, st);
 }
 
 // ------------------------------------------------------------------------------- attention launch

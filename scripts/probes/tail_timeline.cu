@@ -1,4 +1,5 @@
 // Probe: SM-clock timeline of the fused block-tail kernel, CTA 0 (S1 shape).
+#define DDC_PROBE_TIMING 1
 #include "../../ddim_cold_b200/csrc/ddimcold.cu"
 #include <cstdio>
 int main() {
