@@ -48,7 +48,8 @@ struct BlockTailParams {
     const float* lnn_b;
     float ln_eps;
     long long* dbg;          // probes only: [role 2][64] SM clock stamps of CTA 0, [128..] wait accounting
-    int flags;               // probes only: bit 0 = L2-prefetch the next tile's O / residual rows (measured: no gain)
+    int flags;               // tuning: bit 0 = L2-prefetch the next tile's O / residual rows (measured: no gain);
+                             //         bit 1 = L2 eviction hints (weights evict_last; O, residual, X evict_first)
     int stagger;             // SM cycles by which CTA pairs with a spare round start late (0 = off), see the kernel
 };
 
@@ -181,15 +182,21 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         if (lane == 0) {
             const uint32_t me = warp == 0 ? 0u : 1u;
             uint32_t bit = 0, tc = 0;
+            const bool hint = (p.flags & 2) != 0;
+            const uint64_t pol_w = l2_policy_evict_last(), pol_a = l2_policy_evict_first();
             auto load_w = [&](const CUtensorMap* tm, int kcol, int row0) {
                 if ((bit & 1u) == me) {
                     const uint32_t stage = bit % static_cast<uint32_t>(p.stages);
                     const uint32_t phase = (bit / static_cast<uint32_t>(p.stages)) & 1u;
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * kStageBytes);
-                    for (uint32_t i = 0; i < gk; ++i)
-                        tma_load_2d_pair(ring + static_cast<size_t>(stage) * kStageBytes + i * kWBytes, tm, &full_bar[stage],
-                                         kcol + static_cast<int>(i) * 64, row0 + static_cast<int>(crank) * 64);
+                    for (uint32_t i = 0; i < gk; ++i) {
+                        uint8_t* dst = ring + static_cast<size_t>(stage) * kStageBytes + i * kWBytes;
+                        if (hint) tma_load_2d_pair_hint(dst, tm, &full_bar[stage], kcol + static_cast<int>(i) * 64,
+                                                        row0 + static_cast<int>(crank) * 64, pol_w);
+                        else tma_load_2d_pair(dst, tm, &full_bar[stage], kcol + static_cast<int>(i) * 64,
+                                              row0 + static_cast<int>(crank) * 64);
+                    }
                 }
                 ++bit;
             };
@@ -198,7 +205,8 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 mbar_wait(aempty_bar, (tc & 1) ^ 1);                 // fc1 of the previous tile has read Abuf
                 for (int kb = static_cast<int>(me); kb < KB; kb += 2) {
                     if (leader) mbar_arrive_expect_tx(&afull_bar[kb], 2 * G2_A_KB_BYTES);
-                    tma_load_2d_pair(abuf + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmO, &afull_bar[kb], kb * 64, m0);
+                    if (hint) tma_load_2d_pair_hint(abuf + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmO, &afull_bar[kb], kb * 64, m0, pol_a);
+                    else tma_load_2d_pair(abuf + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmO, &afull_bar[kb], kb * 64, m0);
                 }
                 for (int n = 0; n < NB; ++n)
                     for (int kb = 0; kb < KB; kb += p.gk) load_w(&tmWp, kb * 64, n * BT_BN);
@@ -321,6 +329,8 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         float* red_mean = red + hf * 128 + trow;                // [2 stats][NG groups][128 rows]
         float* red_m2 = red + NG * 128 + hf * 128 + trow;
         uint32_t tc = 0, g = 0, ri = 0, res_phase = 0;
+        const bool hint = (p.flags & 2) != 0;
+        const uint64_t pol_x = l2_policy_evict_first();
 
         // LayerNorm statistics in one pass over the data: each group accumulates sum and sum of squares of its part of
         // the row around a shift K (the first value it sees, so nothing cancels), turns them into (mean, M2) of that
@@ -357,7 +367,8 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 bulk_wait_read<0>();               // the previous tile's X / XN stores have read the staging slots
                 for (int k = 0; k < SL && k < nper; ++k) {               // all of the group's slots in flight
                     mbar_arrive_expect_tx(&my_res[k], G2_GSLOT_BYTES);
-                    tma_load_2d(gslots + k * G2_GSLOT_BYTES, &tmXld, &my_res[k], (hf + NG * k) * 32, m0);
+                    if (hint) tma_load_2d_hint(gslots + k * G2_GSLOT_BYTES, &tmXld, &my_res[k], (hf + NG * k) * 32, m0, pol_x);
+                    else tma_load_2d(gslots + k * G2_GSLOT_BYTES, &tmXld, &my_res[k], (hf + NG * k) * 32, m0);
                 }
             }
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 0);
@@ -405,7 +416,8 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     named_bar_sync(gbar, 128);     // every warp of the group has read the slot before it is refilled
                     if (gleader) {
                         mbar_arrive_expect_tx(&my_res[s], G2_GSLOT_BYTES);
-                        tma_load_2d(slot, &tmXld, &my_res[s], (c + NG * SL) * 32, m0);
+                        if (hint) tma_load_2d_hint(slot, &tmXld, &my_res[s], (c + NG * SL) * 32, m0, pol_x);
+                        else tma_load_2d(slot, &tmXld, &my_res[s], (c + NG * SL) * 32, m0);
                     }
                 }
             }
@@ -529,7 +541,8 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 fence_proxy_async_smem();
                 named_bar_sync(gbar, 128);
                 if (gleader && m0 < p.M) {
-                    tma_store_2d(&tmXst, slot, n0, m0);
+                    if (hint) tma_store_2d_hint(&tmXst, slot, n0, m0, pol_x);
+                    else tma_store_2d(&tmXst, slot, n0, m0);
                     bulk_commit();
                 }
             }

@@ -198,7 +198,7 @@ static int launch_block_tail_ng(const CUtensorMap& tmO, const CUtensorMap& tmWp,
     // Two K blocks per ring stage: the stage handshake (full barrier -> MMA -> pair commit -> empty barrier) costs about
     // 500 cycles whatever it carries (scripts/probes/pair_ring_probe.cu), so 16 KB stages stream W twice as fast as 8 KB.
     p.gk = env_int("DDC_TAIL_GK", 2) == 1 ? 1 : 2;
-    p.flags = env_int("DDC_TAIL_FLAGS", 0);
+    p.flags = env_int("DDC_TAIL_FLAGS", 2);                  // L2 eviction hints on (bit 1), next-tile L2 prefetch off (bit 0)
     p.stagger = env_int("DDC_TAIL_STAGGER", 115 * p.C);      // ~3/4 of a tile in SM cycles (measured ~58k per tile at C = 384)
     int stages = static_cast<int>((227 * 1024 - static_cast<long>(block_tail_smem_bytes(p.C, 0, 1))) / (p.gk * 64 * 128));
     if (stages > 8) stages = 8;
