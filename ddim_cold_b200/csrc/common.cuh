@@ -5,6 +5,7 @@
 
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -385,6 +386,25 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
         asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
     }
     return r;
+}
+
+// four 8x8 b16 matrices from registers to shared memory (lane l supplies the address of row l%8 of matrix l/8);
+// after ldmatrix.trans this writes the transposed tiles
+__device__ __forceinline__ void stmatrix_x4(uint32_t addr, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3) {
+    asm volatile("stmatrix.sync.aligned.m8n8.x4.shared.b16 [%0], {%1, %2, %3, %4};"
+                 ::"r"(addr), "r"(r0), "r"(r1), "r"(r2), "r"(r3) : "memory");
+}
+
+// 16-bit pair / scalar -> fp32 (bf16: the value IS the upper half of the fp32 word)
+template <bool F16>
+__device__ __forceinline__ float2 unpack2(uint32_t w) {
+    if (F16) return __half22float2(*reinterpret_cast<const __half2*>(&w));
+    return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xFFFF0000u));
+}
+template <bool F16>
+__device__ __forceinline__ float unpack1(uint16_t v) {
+    if (F16) return __half2float(*reinterpret_cast<const __half*>(&v));
+    return __uint_as_float(static_cast<uint32_t>(v) << 16);
 }
 
 // Exact-erf GELU (nn.GELU() default, approximate='none'; ViT.py:75,80) -- the erf form, not the tanh one.

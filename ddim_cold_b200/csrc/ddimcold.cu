@@ -16,6 +16,7 @@
 #include "elementwise.cuh"
 #include "gemm2.cuh"
 #include "block_tail.cuh"
+#include "attention_tc.cuh"
 
 using namespace ddc;
 
@@ -252,7 +253,26 @@ static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads
     const int lk_pad = (L + KC - 1) / KC * KC;
     const size_t gsmem = att_group_smem_bytes(L, KC);
     const size_t ssmem = att_stream_smem_bytes(L, KC);
-    if (C % 64 == 0 && L <= KC && lk_pad <= 256 && ssmem <= 75 * 1024 && !env_int("DDC_ATT_ONESHOT", 0)) {
+    if (D == 32 && attention_tc_usable(L, C, heads) && env_int("DDC_ATT_TC", 0)) {
+        // tcgen05 path: both contractions as UMMA, softmax from TMEM (attention_tc.cuh).  Opt-in: correct, but at
+        // L = 65 its per-item chain (TMA -> S MMA -> softmax -> P*V MMA -> output, ~5k cycles with two items in
+        // flight per SM) measures 70 us against 58 us for the warp-level kernel, which keeps 15 items in flight.
+        static int tc_attr_mask = 0;
+        if (!(tc_attr_mask & (1 << dev))) {
+            CK(cudaFuncSetAttribute(attention_tc_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATC_SMEM_BYTES));
+            tc_attr_mask |= (1 << dev);
+        }
+        CUtensorMap tmq, tmkv;
+        TRY(make_tmap(&tmq, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, 64));
+        TRY(make_tmap(&tmkv, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, ATC_KEYS));
+        const int n_hg = C / 64;
+        const int n_items = B * n_hg;
+        const uint32_t magic = n_hg > 1 ? static_cast<uint32_t>((1ull << 32) / static_cast<uint32_t>(n_hg)) + 1u : 0u;
+        int grid = 2 * num_sms();
+        if (grid > n_items) grid = n_items;
+        CK(launch_chain(attention_tc_kernel<F16>, dim3(grid), dim3(ATC_THREADS), static_cast<size_t>(ATC_SMEM_BYTES), st, 1, tmq, tmkv,
+                        qkv, out, L, C, n_items, magic, scale_log2e));
+    } else if (C % 64 == 0 && L <= KC && lk_pad <= 256 && ssmem <= 75 * 1024 && !env_int("DDC_ATT_ONESHOT", 0)) {
         // persistent CTAs, next item's tiles in flight while this one is computed
         CUtensorMap tm;
         TRY(make_tmap(&tm, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, lk_pad));
