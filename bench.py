@@ -318,7 +318,7 @@ def main():
     whole_tf = flops_img_step * B * n_steps * args.steps * world / (dev_ms / 1e3) / 1e12 / world
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this workload
     # (S1, 1024 images per GPU); other workloads were not captured -> null
-    ncu_traffic = {4: (250.5e6, "profiles/r01c_ncu_full.txt"), 2: (146.8e6, "profiles/r01b_ncu_full.txt")}
+    ncu_traffic = {4: (250.5e6, "profiles/r01d_ncu_full.txt"), 2: (163.7e6, "profiles/r01d_ncu_full.txt")}
     traffic, traffic_src = (ncu_traffic[dom] if (args.shape == "s1" and B == 1024 and (dom != 4 or fused_tail))
                             else (None, None))
     line = {
