@@ -181,7 +181,7 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
 
 // ------------------------------------------------------------------------------- fused block tail launch
 static bool block_tail_usable(int M, int C, int bn_row) {
-    return C % 128 == 0 && C <= 384 && bn_row == 128 && (M + G2_BM - 1) / G2_BM >= 2 && !env_int("DDC_NO_FUSE", 0);
+    return C % 128 == 0 && C <= 384 && bn_row == 128 && (M + G2_BM - 1) / G2_BM >= 1 && !env_int("DDC_NO_FUSE", 0);
 }
 
 template <bool F16, int NG>
@@ -551,7 +551,7 @@ extern "C" int ddc_plan_set_operand_format(ddc_plan* plan, int32_t fmt) {
 extern "C" int ddc_launches_per_step(const ddc_plan* plan) {
     if (plan == nullptr) return 0;
     // patchify, embed GEMM, per block {qkv GEMM, attention, fused tail} or {qkv, attention, proj, fc1, fc2}, head GEMM,
-    // head_ddim (the fused tail needs at least two 128-row tiles; smaller calls fall back to the separate kernels)
+    // head_ddim (the fused tail needs embed_dim % 128 == 0 and <= 384; other shapes use the separate kernels)
     const bool fused = block_tail_usable(plan->maxB * plan->L, plan->C, plan->bn_row);
     return 2 + (fused ? 3 : 5) * plan->sh.depth + 2;
 }

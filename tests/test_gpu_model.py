@@ -108,6 +108,19 @@ def test_deterministic_and_batch_invariant(tiny):
     assert torch.equal(a, b) and torch.equal(a[1:2], c)
 
 
+def test_batch_invariant_on_the_fused_path():
+    """The same check on a shape that takes the fused block tail, the tcgen05 GEMM pair kernels and the 65-token
+    attention (embed 128, L = 65): one sample alone (a single, half-empty tile pair) == the same sample in a batch."""
+    from oracle import ddim_oracle as O
+    sh = O.Shape(32, 32, 4, 128, 2, 4)
+    m = build(sh, O.synth_state_dict(sh, seed=3, rich=True))
+    x = torch.from_numpy(O.synth_noise((5, 3, 32, 32), seed=9))
+    a = m.sampler("cuda", 200, 5, noise=x)
+    c = m.sampler("cuda", 200, 1, noise=x[3:4])
+    d = m.sampler("cuda", 200, 2, noise=x[3:5])
+    assert torch.equal(a[3:4], c) and torch.equal(a[3:5], d)
+
+
 def test_sequence_cold_d2d_tiny(tiny):
     from oracle import ddim_oracle as O
     g, sd, m = tiny
