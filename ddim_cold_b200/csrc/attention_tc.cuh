@@ -26,8 +26,7 @@ constexpr int ATC_Q_BYTES = 2 * 64 * 128;                 // the 64 query rows, 
 constexpr int ATC_KV_BYTES = ATC_KEYS * 128;              // 10 KB, a multiple of 1024
 constexpr int ATC_VT_BYTES = 2 * 2 * 32 * 128;            // [head][K block][32 rows x 128 B]
 constexpr int ATC_P_BYTES = 2 * 128 * 128;                // [K block][128 rows x 128 B]
-constexpr int ATC_OUT_BYTES = 64 * 128;
-constexpr int ATC_SMEM_BYTES = 1024 + ATC_Q_BYTES + 2 * ATC_KV_BYTES + ATC_VT_BYTES + ATC_P_BYTES + ATC_OUT_BYTES + 256;
+constexpr int ATC_SMEM_BYTES = 1024 + ATC_Q_BYTES + 2 * ATC_KV_BYTES + ATC_VT_BYTES + ATC_P_BYTES + 256;
 
 inline bool attention_tc_usable(int L, int C, int heads) {
     return heads > 0 && C % heads == 0 && C / heads == 32 && C % 64 == 0 && L == 65;     // 64 tile rows + one side row
@@ -56,8 +55,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ,      // qkv [rows, 
     uint8_t* Vs = Ks + ATC_KV_BYTES;
     uint8_t* VT = Vs + ATC_KV_BYTES;
     uint8_t* Ps = VT + ATC_VT_BYTES;
-    uint8_t* Os = Ps + ATC_P_BYTES;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(Os + ATC_OUT_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(Ps + ATC_P_BYTES);
     uint64_t* full_bar = bars;          // Q, K, V landed (TMA bytes)
     uint64_t* s_bar = bars + 1;         // both S MMAs complete (commit): Q and K no longer read by the tensor core
     uint64_t* rel_bar = bars + 2;       // transposes (4 warps) done with V
