@@ -256,7 +256,7 @@ static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads
     if (D == 32 && attention_tc_usable(L, C, heads) && env_int("DDC_ATT_TC", 0)) {
         // tcgen05 path: both contractions as UMMA, softmax from TMEM (attention_tc.cuh).  Opt-in: correct, but at
         // L = 65 its per-item chain (TMA -> S MMA -> softmax -> P*V MMA -> output, ~5k cycles with two items in
-        // flight per SM) measures 70 us against 58 us for the warp-level kernel, which keeps 15 items in flight.
+        // flight per SM) measures 70 - 160 us against 58 us for the warp-level kernel, which keeps 15 items in flight.
         static int tc_attr_mask = 0;
         if (!(tc_attr_mask & (1 << dev))) {
             CK(cudaFuncSetAttribute(attention_tc_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATC_SMEM_BYTES));
