@@ -272,9 +272,12 @@ attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restr
         int img, hg;
         split(item, img, hg);
         mbar_arrive_expect_tx(&full[s], 3 * tile_bytes);
+        // QKV is read exactly once: stream it through L2 (evict_first) so that the attention output written below and
+        // the weights stay resident for the block tail that follows
+        const uint64_t pol = l2_policy_evict_first();
 #pragma unroll
         for (int m = 0; m < 3; ++m)
-            tma_load_2d(sm + (s * 3 + m) * tile_bytes, &tmQKV, &full[s], m * C + hg * 64, img * L);
+            tma_load_2d_hint(sm + (s * 3 + m) * tile_bytes, &tmQKV, &full[s], m * C + hg * 64, img * L, pol);
     };
     if (threadIdx.x == 0) {
         mbar_init(&full[0], 1);
