@@ -171,6 +171,7 @@ static int launch_gemm2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
     if (smem > 227 * 1024) return fail(DDC_E_INVALID, "gemm: %zu B of shared memory needed", smem);
     p.num_tiles = ((p.M + G2_BM - 1) / G2_BM + cs - 1) / cs * cs;
     p.balanced = (!rowblock && env_int("DDC_BALANCED", 1)) ? 1 : 0;
+    p.dbg_flags |= env_int("DDC_GEMM_FLAGS", 0);          // tuning: 16 = no L2 eviction hints on the operand loads
     if (f16) {
         if (cs == 2) return launch_gemm2_inst<EPI, true, 2>(tmA, tmB, tmO, tmR, tmN, p, smem, st);
         return launch_gemm2_inst<EPI, true, 1>(tmA, tmB, tmO, tmR, tmN, p, smem, st);

@@ -219,16 +219,20 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (lane == 0) {
             const uint32_t me = warp == 0 ? 0u : 1u;
             uint32_t bit = 0, tcount = 0;          // bit: running index of W loads (stage = bit % stages)
+            // L2 priorities: activations are read once (evict_first), the weights by every CTA all the time (evict_last)
+            const bool nohint = (p.dbg_flags & 16) != 0;
+            const uint64_t pol_a = nohint ? l2_policy_evict_normal() : l2_policy_evict_first();
+            const uint64_t pol_w = nohint ? l2_policy_evict_normal() : l2_policy_evict_last();
             for (int tile, nt0, nt1; segment(tcount, tile, nt0, nt1); ++tcount) {
                 const int m0 = tile * G2_BM;
                 for (int kb = static_cast<int>(me); kb < kblocks; kb += 2) {
                     mbar_wait(&aempty_bar[kb], (tcount & 1) ^ 1);
                     if (CS == 1) {
                         mbar_arrive_expect_tx(&afull_bar[kb], G2_A_KB_BYTES);
-                        tma_load_2d(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0);
+                        tma_load_2d_hint(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0, pol_a);
                     } else {      // both CTAs' bytes are credited to the leader's barrier
                         if (leader) mbar_arrive_expect_tx(&afull_bar[kb], CS * G2_A_KB_BYTES);
-                        tma_load_2d_pair(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0);
+                        tma_load_2d_pair_hint(smem_a + static_cast<size_t>(kb) * G2_A_KB_BYTES, &tmA, &afull_bar[kb], kb * G2_BK, m0, pol_a);
                     }
                 }
                 int ntile, na, nb;
@@ -242,12 +246,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                         mbar_wait(&empty_bar[stage], phase ^ 1);
                         if (CS == 1) {
                             mbar_arrive_expect_tx(&full_bar[stage], b_stage_bytes);
-                            tma_load_2d(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
-                                        kb * G2_BK, nt * p.bn);
+                            tma_load_2d_hint(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
+                                             kb * G2_BK, nt * p.bn, pol_w);
                         } else {      // this CTA stages rows [crank*bn/2, +bn/2) of the W tile
                             if (leader) mbar_arrive_expect_tx(&full_bar[stage], CS * b_stage_bytes);
-                            tma_load_2d_pair(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
-                                             kb * G2_BK, nt * p.bn + static_cast<int>(crank) * (p.bn / CS));
+                            tma_load_2d_pair_hint(smem_b + static_cast<size_t>(stage) * b_stage_bytes, &tmB, &full_bar[stage],
+                                                  kb * G2_BK, nt * p.bn + static_cast<int>(crank) * (p.bn / CS), pol_w);
                         }
                     }
                 }
