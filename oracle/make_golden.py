@@ -86,16 +86,7 @@ def ref_trace(model, x_T, k, t_start=None):
     return out
 
 
-def main():
-    torch.set_num_threads(8)
-    ViT, D2D = import_reference()
-    os.makedirs(OUT, exist_ok=True)
-    pin = {"torch": torch.__version__, "numpy": np.__version__, "cases": {}}
-
-    def record(name, value):
-        pin["cases"][name] = value
-        print(f"{name}: {value}")
-
+def gen_tiny(ViT, D2D, record):
     # ------------------------------------------------------------------ TINY: whole API
     sh = O.TINY
     sd = O.synth_state_dict(sh, seed=11, rich=True, gain=4.0)   # gain 4 -> clamp is exercised
@@ -187,6 +178,8 @@ def main():
     fix["d2d_noise_seed"] = np.array(21)
     np.savez_compressed(os.path.join(OUT, "tiny.npz"), **fix)
 
+
+def gen_real(ViT, D2D, record):
     # ------------------------------------------------------------------ S1 / S2: real shapes
     for tag, sh, wseed in (("s1", O.S1, 0), ("s2", O.S2, 1)):
         sd = O.synth_state_dict(sh, seed=wseed, rich=True)
@@ -219,7 +212,108 @@ def main():
         record(f"{tag}.clamp_frac", float(fix["clamp_frac"]))
         np.savez_compressed(os.path.join(OUT, f"{tag}.npz"), **fix)
 
-    with open(os.path.join(OUT, "PIN.json"), "w") as f:
+
+def gen_s3(ViT, D2D, record):
+    # ------------------------------------------------------------------ S3: the declared 200x200 stand-in (L = 626)
+    # Forward at three timesteps (one image each, different t per image -- forward() allows it, ViT.py:204) and a
+    # short free-running sampler, k = 500 (4 steps), N = 1.
+    sh = O.S3
+    sd = O.synth_state_dict(sh, seed=2, rich=True)
+    m = ref_model(ViT, sh, sd)
+    fix = {}
+    x = torch.from_numpy(O.synth_noise((3, 3, sh.img_h, sh.img_w), seed=41))
+    t = torch.tensor([1999, 999, 19])
+    with torch.no_grad():
+        y = m.forward(x, t)
+    fix["fwd_x"], fix["fwd_t"], fix["fwd_y"] = x.numpy(), t.numpy(), y.numpy()
+    record("s3.forward.np32", maxabs(O.forward(sd, sh, x.numpy(), t.numpy(), np.float32), y))
+    record("s3.forward.torchport", maxabs(OT.forward(OT.to_torch_sd(sd), sh, x, t), y))
+    torch.manual_seed(77)
+    x_T = torch.normal(0, 1, (1, 3, sh.img_h, sh.img_w))
+    torch.manual_seed(77)
+    img = quiet(m.sampler, "cpu", 500, 1)
+    tr = ref_trace(m, x_T, 500)
+    assert torch.equal((tr[-1]["x0"] + 1) / 2, img)
+    fix["xT"], fix["samp500_img"] = x_T.numpy(), img.numpy()
+    fix["tap_t"] = np.array([s["t"] for s in tr])
+    for key in ("x_t", "x0", "eps"):
+        fix[f"tap_{key}"] = np.stack([s[key].numpy() for s in tr])
+    record("s3.sampler.k500.np32", maxabs(O.sampler(sd, sh, x_T.numpy(), 500, np.float32), img))
+    record("s3.sampler.k500.torchport", maxabs(OT.sampler(OT.to_torch_sd(sd), sh, x_T, 500), img))
+    np.savez_compressed(os.path.join(OUT, "s3.npz"), **fix)
+
+
+def gen_fused(ViT, D2D, record):
+    # ------------------------------------------------------------------ FUSED: 32x32 / p4 / C128 / depth 2 / 4 heads
+    # L = 65 tokens, head_dim 32, embed_dim % 128 == 0: on the GPU this shape takes the fused block tail, the CTA-pair
+    # GEMMs and the 65-token attention -- S1's code path at fixture size.  Every loop of the class API is recorded
+    # from the reference here (TINY covers the same API on the separate-kernel path).
+    sh = O.Shape(32, 32, 4, 128, 2, 4)
+    sd = O.synth_state_dict(sh, seed=3, rich=True, gain=2.0)
+    m = ref_model(ViT, sh, sd)
+    md = ref_model(D2D, sh, sd)
+    fix = {}
+    torch.manual_seed(15)
+    x_T = torch.normal(0, 1, (3, 3, sh.img_h, sh.img_w))
+    torch.manual_seed(15)
+    with torch.no_grad():
+        seq = quiet(m.diffusion_sequence, "cpu", 400, 3)
+    fix["seq400_xT"], fix["seq400_imgs"] = x_T.numpy(), torch.stack(seq).numpy()
+    record("fused.diffusion_sequence.k400.np32", maxabs(np.stack(O.diffusion_sequence(sd, sh, x_T.numpy(), 400)), fix["seq400_imgs"]))
+    torch.manual_seed(15)
+    img = quiet(m.sampler, "cpu", 100, 3)
+    fix["samp100_img"] = img.numpy()
+    record("fused.sampler.k100.np32", maxabs(O.sampler(sd, sh, x_T.numpy(), 100, np.float32), img))
+    torch.manual_seed(19)
+    z = torch.normal(0, 1, (4, 3))
+    x_init = z.unsqueeze(2).unsqueeze(3).expand(-1, -1, sh.img_h, sh.img_w)
+    torch.manual_seed(19)
+    cimg = quiet(md.cold_sampler, "cpu", 10, 4)
+    torch.manual_seed(19)
+    cseq = quiet(md.cold_diffusion_sequence, "cpu", 4)
+    fix["cold_z"], fix["cold_img"], fix["cold_seq"] = z.numpy(), cimg.numpy(), torch.stack(cseq).numpy()
+    oc = O.cold_sequence(sd, sh, x_init.numpy())
+    record("fused.cold_sampler.np32", maxabs(oc[-1], cimg))
+    record("fused.cold_sequence.np32", maxabs(np.stack(oc), fix["cold_seq"]))
+    draft = torch.from_numpy(O.synth_draft(sh))
+    noise = torch.from_numpy(O.synth_noise((3, 3, sh.img_h, sh.img_w), seed=23))
+    for t_start in (1599, 1999):
+        alpha = 1 - math.sqrt(t_start / 2000)
+        x = noise * math.sqrt(1 - alpha) + draft * math.sqrt(alpha)
+        tr = ref_trace(md, x, 10, t_start=t_start)
+        img = (tr[-1]["x0"] + 1) / 2
+        fix[f"d2d{t_start}_img"] = img.numpy()
+        record(f"fused.d2d.{t_start}.np32", maxabs(O.d2d(sd, sh, noise.numpy(), draft.numpy(), t_start), img))
+    fix["d2d_noise_seed"] = np.array(23)
+    np.savez_compressed(os.path.join(OUT, "fused.npz"), **fix)
+
+
+CASES = {"tiny": gen_tiny, "real": gen_real, "s3": gen_s3, "fused": gen_fused}
+
+
+def main(argv=None):
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", nargs="*", choices=list(CASES), default=list(CASES),
+                    help="regenerate only these fixture groups (PIN.json entries of the others are kept)")
+    args = ap.parse_args(argv)
+    torch.set_num_threads(8)
+    ViT, D2D = import_reference()
+    os.makedirs(OUT, exist_ok=True)
+    pin_path = os.path.join(OUT, "PIN.json")
+    pin = {"cases": {}}
+    if os.path.exists(pin_path) and set(args.only) != set(CASES):
+        with open(pin_path) as f:
+            pin = json.load(f)
+    pin["torch"], pin["numpy"] = torch.__version__, np.__version__
+
+    def record(name, value):
+        pin["cases"][name] = value
+        print(f"{name}: {value}")
+
+    for name in args.only:
+        CASES[name](ViT, D2D, record)
+    with open(pin_path, "w") as f:
         json.dump(pin, f, indent=1, sort_keys=True)
     worst = max(v for k, v in pin["cases"].items() if "clamp" not in k)
     print("worst oracle-vs-reference deviation:", worst)

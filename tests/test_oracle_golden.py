@@ -123,3 +123,36 @@ def test_real_shapes_taps(golden, tag, sh, seed):
         assert maxabs(xn, g["tap_x_next"][j]) < TOL
         y = torch.clamp(OT.forward(sdt, sh, torch.from_numpy(x_t), torch.tensor([int(t)])), -1, 1)
         assert maxabs(y.numpy(), g["tap_x0"][j]) < TOL
+
+
+FUSED = O.Shape(32, 32, 4, 128, 2, 4)      # the shape whose GPU run takes the fused block tail + 65-token attention
+
+
+def test_fused_shape_loops(golden):
+    """Every loop of the class API on the fixture-sized twin of S1's code path (tests/golden/fused.npz)."""
+    g = golden("fused")
+    sd = O.synth_state_dict(FUSED, seed=3, rich=True, gain=2.0)
+    assert maxabs(np.stack(O.diffusion_sequence(sd, FUSED, g["seq400_xT"], 400)), g["seq400_imgs"]) < TOL
+    assert maxabs(O.sampler(sd, FUSED, g["seq400_xT"], 100), g["samp100_img"]) < TOL
+    x_init = np.broadcast_to(g["cold_z"][:, :, None, None], (4, 3, 32, 32))
+    seq = O.cold_sequence(sd, FUSED, x_init)
+    assert maxabs(np.stack(seq), g["cold_seq"]) < TOL and maxabs(seq[-1], g["cold_img"]) < TOL
+    noise = O.synth_noise((3, 3, 32, 32), seed=int(g["d2d_noise_seed"]))
+    draft = O.synth_draft(FUSED)
+    for t0 in (1599, 1999):
+        assert maxabs(O.d2d(sd, FUSED, noise, draft, t0), g[f"d2d{t0}_img"]) < TOL
+
+
+def test_s3_forward_and_taps(golden):
+    """S3 (declared 200x200 stand-in, L = 626): the torch port against the reference's forward at three timesteps
+    and against the first step of the recorded k = 500 trajectory (the numpy oracle on one image to keep it quick)."""
+    g = golden("s3")
+    sd = O.synth_state_dict(O.S3, seed=2, rich=True)
+    sdt = OT.to_torch_sd(sd)
+    y = OT.forward(sdt, O.S3, torch.from_numpy(g["fwd_x"]), torch.from_numpy(g["fwd_t"]))
+    assert maxabs(y.numpy(), g["fwd_y"]) < TOL
+    assert maxabs(O.forward(sd, O.S3, g["fwd_x"][:1], g["fwd_t"][:1]), g["fwd_y"][:1]) < TOL
+    x0 = torch.clamp(OT.forward(sdt, O.S3, torch.from_numpy(g["tap_x_t"][0]), torch.tensor([int(g["tap_t"][0])])), -1, 1)
+    assert maxabs(x0.numpy(), g["tap_x0"][0]) < TOL
+    eps, _ = O.ddim_update(g["tap_x_t"][0], g["tap_x0"][0], int(g["tap_t"][0]), 500)
+    assert maxabs(eps, g["tap_eps"][0]) < TOL
