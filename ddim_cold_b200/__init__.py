@@ -2,7 +2,7 @@
 ``ViT.py`` / ``ViT_draft2drawing.py`` model class.  See DESIGN.md and INTEGRATION.md."""
 from .vit import DiffusionVisionTransformer
 from .checkpoint import infer_shape, load_checkpoint, model_from_yaml
-from .shard import shard_bounds, sample_sharded
+from .shard import SharedHostImages, shard_bounds, sample_sharded
 
 __all__ = ["DiffusionVisionTransformer", "infer_shape", "load_checkpoint", "model_from_yaml",
-           "shard_bounds", "sample_sharded"]
+           "shard_bounds", "sample_sharded", "SharedHostImages"]

@@ -53,9 +53,11 @@ SIGNATURES = {
     "ddc_plan_set_operand_format": (C.c_int, [_vp, _i32]),
     "ddc_k_gemm": (C.c_int, [_i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
     "ddc_k_gemm_resid_ln": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ddc_k_embed": (C.c_int, [_i32] * 6 + [_vp] * 10),
     "ddc_k_block_tail": (C.c_int, [_i32, _i32, _i32] + [_vp] * 14),
     "ddc_k_attention": (C.c_int, [_i32, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "ddc_k_patchify": (C.c_int, [_i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "ddc_k_affine": (C.c_int, [_vp, _vp, _sz, C.c_float, C.c_float, _vp]),
     "ddc_k_head_ddim": (C.c_int, [_vp, _i32, _vp, _i32, _i32, _i32, _i32, C.POINTER(Step), _vp, _vp, _vp]),
 }
 

@@ -101,7 +101,7 @@ def build_model(ckpt, config, shape, heads, seed) -> DiffusionVisionTransformer:
 @click.option("--seq_n", default=6, show_default=True, help="Rows of the denoising-sequence sheet (0 = skip it).")
 @click.option("--seq_k", default=100, show_default=True, help="Step jump of the denoising-sequence sheet.")
 @click.option("--seed", default=None, type=int, help="torch.manual_seed before random init and before sampling.")
-@click.option("--operand_format", default="bf16", type=click.Choice(["bf16", "fp16"]), show_default=True)
+@click.option("--operand_format", default="fp16", type=click.Choice(["fp16", "bf16"]), show_default=True)
 def main(sample_n, acc_k, ckpt, config, shape, heads, out_dir, seq_n, seq_k, seed, operand_format):
     """Sample with the B200 path and write denoise_sequence.png and samples.png (headless ViT.py main())."""
     if not torch.cuda.is_available():

@@ -150,7 +150,7 @@ static int launch_gemm2_inst(const CUtensorMap& tmA, const CUtensorMap& tmB, con
     return DDC_OK;
 }
 
-// W tiles are multicast to the `cs` CTAs of a cluster; tmB's box must hold bn/cs rows.
+// Each CTA of a pair stages its own bn/cs rows of every W tile (tmB's box holds bn/cs rows); the pair's MMAs read both.
 static int gemm_cluster_size(int M) {
     const int forced = env_int("DDC_CLUSTER", 0);        // tuning aid
     if (forced == 1 || forced == 2) return forced;
@@ -591,6 +591,10 @@ extern "C" int ddc_pack_weights(ddc_plan* pl, const float* const* t, int32_t n_t
     copy(e[0], pl->lnf_g, C);  copy(e[1], pl->lnf_b, C);
     pack(e[2], pl->w_head, P, C, C);  copy(e[3], pl->b_head, P);
     CK(cudaGetLastError());
+    // The step-path kernels are launched with programmatic dependent launch and read weights (bias, LayerNorm affine)
+    // in their prologue, BEFORE they wait for their predecessor.  Packing is rare, so make it a full stop: once this
+    // returns, every packed byte is visible to anything launched later, on any stream.
+    CK(cudaStreamSynchronize(st));
     pl->packed = true;
     return DDC_OK;
 }
@@ -665,6 +669,7 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     g.M = M; g.N = C; g.K = pl->Kp; g.bn = pl->bn_row; g.stages = pick_stages2(g.K, g.N, g.bn / cs, true);
     g.ln_g = l0.ln1_g; g.ln_b = l0.ln1_b; g.ln_eps = 1e-5f;
     g.posb = pl->posb; g.L = L; g.time_tab = pl->time_tab; g.t_img = t_img; g.tbl = pl->tbl; g.cur = pl->ctr; g.B = B;
+    g.T = s.total_steps;
     TRY((launch_gemm2<R_EMBED>(pl->tm_Ap, pl->tm_wpatch[cs - 1], pl->st_X, pl->tm_posb, pl->st_XN, g, f16, cs, st)));
     MARK(KC_EMBED);
     for (int i = 0; i < s.depth; ++i) {
@@ -736,9 +741,8 @@ extern "C" int ddc_forward(ddc_plan* pl, const float* x, const int32_t* t, int32
 
 // ------------------------------------------------------------------------------- forward without any allocation
 // Some hosts may not allocate device memory at the moment they need a prediction: a serving loop that has
-// handed its whole memory budget to another framework's pool, code between cudaStreamBeginCapture and
-// EndCapture (cudaMalloc is illegal there), or a latency-critical thread for which cudaMalloc's implicit
-// device synchronisation is unacceptable.  For them the activations of one forward pass can live in this
+// handed its whole memory budget to another framework's pool, or a latency-critical thread for which
+// cudaMalloc's implicit device synchronisation is unacceptable.  For them the activations of one forward pass can live in this
 // fixed array instead of a caller-provided work arena.  It is part of the library image: every GPU that
 // loads the library carries it until the process exits, which is why it is kept modest.
 #define DDC_FIXED_SCRATCH_BYTES (32u << 20)
@@ -866,6 +870,9 @@ extern "C" int ddc_profile_steps(ddc_plan* pl, float* x, int32_t batch, const dd
     if (x == nullptr || host_table == nullptr || class_ms == nullptr || class_launches == nullptr)
         return fail(DDC_E_INVALID, "NULL argument");
     if (n_steps <= 0 || n_steps > pl->sh.total_steps) return fail(DDC_E_INVALID, "n_steps %d", n_steps);
+    for (int i = 0; i < n_steps; ++i)
+        if (host_table[i].t < 0 || host_table[i].t >= pl->sh.total_steps)
+            return fail(DDC_E_INVALID, "step %d: t=%d outside the time_embed table", i, host_table[i].t);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CK(cudaSetDevice(pl->device));
     CK(cudaMemcpyAsync(pl->tbl, host_table, sizeof(StepEntry) * n_steps, cudaMemcpyHostToDevice, st));
@@ -1044,6 +1051,30 @@ extern "C" int ddc_k_gemm_resid_ln(int32_t fmt, int32_t M, int32_t C, int32_t K,
     return launch_gemm2<R_RESID>(tmA, tmB, tmO, tmR, tmN, p, fmt == 1, cs, st);
 }
 
+extern "C" int ddc_k_embed(int32_t fmt, int32_t batch, int32_t L, int32_t C, int32_t Kp, int32_t total_steps, const void* ap,
+                           const void* w_patch, const float* posb, const float* time_tab, const int32_t* t_img,
+                           const float* ln_g, const float* ln_b, float* x, void* xn, void* stream) {
+    if (!ap || !w_patch || !posb || !time_tab || !t_img || !ln_g || !ln_b || !x || !xn) return fail(DDC_E_INVALID, "NULL tensor");
+    if (batch <= 0 || L <= 1 || C <= 0 || C % 64 != 0 || C > 512 || Kp <= 0 || Kp % 64 != 0 || Kp > 512 || total_steps <= 0)
+        return fail(DDC_E_INVALID, "embed: bad sizes (batch=%d L=%d C=%d Kp=%d)", batch, L, C, Kp);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int M = batch * L;
+    const uint64_t Mp = (static_cast<uint64_t>(M) + G2_BM - 1) / G2_BM * G2_BM;
+    const int bn = pick_bn_row(C);
+    const int cs = gemm_cluster_size(M);
+    CUtensorMap tmA, tmB, tmO, tmR, tmN;
+    TRY(make_tmap(&tmA, false, ap, Mp, Kp, G2_BM));
+    TRY(make_tmap(&tmB, false, w_patch, C, Kp, bn / cs));
+    TRY(make_tmap(&tmO, true, x, M, C, G2_BM));
+    TRY(make_tmap(&tmR, true, posb, static_cast<uint64_t>(L) + 127, C, G2_BM));
+    TRY(make_tmap(&tmN, false, xn, M, C, G2_BM));
+    Gemm2Params g{};
+    g.M = M; g.N = C; g.K = Kp; g.bn = bn; g.stages = pick_stages2(Kp, C, bn / cs, true);
+    g.ln_g = ln_g; g.ln_b = ln_b; g.ln_eps = 1e-5f;
+    g.posb = posb; g.L = L; g.time_tab = time_tab; g.t_img = t_img; g.B = batch; g.T = total_steps;
+    return launch_gemm2<R_EMBED>(tmA, tmB, tmO, tmR, tmN, g, fmt == 1, cs, st);
+}
+
 extern "C" int ddc_k_block_tail(int32_t fmt, int32_t M, int32_t C, const void* O, const void* Wproj, const float* b_proj,
                                 const float* ln2_g, const float* ln2_b, const void* Wfc1, const float* b_fc1,
                                 const void* Wfc2, const float* b_fc2, const float* lnn_g, const float* lnn_b, float* x,
@@ -1085,6 +1116,19 @@ extern "C" int ddc_k_patchify(int32_t fmt, const float* x, void* ap, int32_t bat
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CK(fmt == 1 ? launch_patchify<true>(x, static_cast<bf16*>(ap), batch, H, W, patch, L, Kp, nullptr, st)
                 : launch_patchify<false>(x, static_cast<bf16*>(ap), batch, H, W, patch, L, Kp, nullptr, st));
+    return DDC_OK;
+}
+
+extern "C" int ddc_k_affine(const float* in, float* out, size_t n, float add, float mul, void* stream) {
+    if (in == nullptr || out == nullptr) return fail(DDC_E_INVALID, "NULL tensor");
+    if ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) return fail(DDC_E_INVALID, "affine: 16-byte alignment");
+    if (n == 0) return DDC_OK;
+    size_t blocks = (n / 4 + 255) / 256;
+    const size_t cap = static_cast<size_t>(num_sms()) * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks == 0) blocks = 1;
+    affine_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(in, out, n, add, mul);
+    CK(cudaGetLastError());
     return DDC_OK;
 }
 

@@ -322,6 +322,20 @@ __global__ void pack_posb_kernel(const float* __restrict__ pos, const float* __r
     }
 }
 
+// out = (in + add) * mul, float4 lanes.  The samplers return (x0 + 1) / 2 (ViT.py:237): one pass on the device
+// before the copy back instead of a 50 MB pass on the host.  Not on the step chain (plain launch, no PDL).
+__global__ void __launch_bounds__(256) affine_kernel(const float* __restrict__ in, float* __restrict__ out, size_t n,
+                                                     float add, float mul) {
+    const size_t n4 = n >> 2;
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+        const float4 v = reinterpret_cast<const float4*>(in)[i];
+        reinterpret_cast<float4*>(out)[i] = make_float4((v.x + add) * mul, (v.y + add) * mul, (v.z + add) * mul, (v.w + add) * mul);
+    }
+    for (size_t i = (n4 << 2) + blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n; i += stride)
+        out[i] = (in[i] + add) * mul;
+}
+
 __global__ void copy_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, size_t n) {
     for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
          i += static_cast<size_t>(gridDim.x) * blockDim.x)

@@ -59,6 +59,7 @@ struct Gemm2Params {
     const StepEntry* tbl;
     const int* cur;
     int B;
+    int T;                   // R_EMBED: rows of time_tab; a per-image t outside [0, T) is clamped into it (0 = unchecked)
     int balanced;            // streaming flavours: split (M tile, N tile) units evenly over the CTA pairs
     int dbg_flags;           // probes only: 1 = no X store, 2 = no residual load, 4 = no tmem_st, 8 = skip LN passes
     long long* dbg;          // optional timeline buffer (probes only): [cta < 2][role 4][64] SM clock stamps
@@ -454,7 +455,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
                 if (EPI == R_EMBED && p.t_img != nullptr) {
                     int b = row / p.L;
                     if (b > p.B - 1) b = p.B - 1;
-                    embed_time = p.time_tab + static_cast<size_t>(p.t_img[b]) * p.N;
+                    int tt = p.t_img[b];             // the host class raises IndexError first; a raw C-ABI caller gets a clamp
+                    if (p.T > 0) tt = tt < 0 ? 0 : (tt >= p.T ? p.T - 1 : tt);
+                    embed_time = p.time_tab + static_cast<size_t>(tt) * p.N;
                 }
                 // residual rows: X[m0 ..] (R_RESID) or the position rows of these tokens, (m0 % L) + r in the table
                 const int r_row = EPI == R_EMBED ? m0 % p.L : m0;

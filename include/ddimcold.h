@@ -73,8 +73,10 @@ int ddc_cold_table(ddc_step* host_table, int32_t capacity, int32_t* n_steps);
 /* Arena sizes in bytes for `shape` at up to `max_batch` images per call. */
 int ddc_arena_bytes(const ddc_shape* shape, int32_t max_batch, size_t* weight_bytes, size_t* work_bytes);
 
-/* Create a plan over caller-owned device arenas (256-byte aligned; the work arena must be
- * zero-filled by the caller once before first use). */
+/* Create a plan over caller-owned device arenas (256-byte aligned).  The work arena needs no
+ * particular initial contents: every row below batch*L of every buffer is written by the kernel
+ * that precedes its first reader, rows above it are computed on but never stored (zero-filling it
+ * once keeps sanitizers quiet about the padding rows and is what the Python class does). */
 int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_t device, void* weight_arena, size_t weight_bytes,
                     void* work_arena, size_t work_bytes, ddc_plan** out);
 int ddc_plan_destroy(ddc_plan* plan);
@@ -91,11 +93,16 @@ int ddc_plan_set_operand_format(ddc_plan* plan, int32_t fmt);
  * patch_embed.proj.bias, time_embed.weight, then per block norm1.{weight,bias},
  * attn.qkv.{weight,bias}, attn.proj.{weight,bias}, norm2.{weight,bias}, mlp.fc1.{weight,bias},
  * mlp.fc2.{weight,bias}, then norm.{weight,bias}, head.{weight,bias}
- * (9 + 12*depth entries; reference ViT.py:169-183). */
+ * (9 + 12*depth entries; reference ViT.py:169-183).  Synchronises `stream` before returning, so the
+ * packed weights are visible to every later launch (the step kernels read weights in their
+ * prologue, ahead of the programmatic-dependent-launch wait). */
 int ddc_pack_weights(ddc_plan* plan, const float* const* tensors, int32_t n_tensors, void* stream);
 
 /* One evaluation of the x0 predictor: out = forward(x, t), unclamped
- * (reference ViT.py:208-218).  x, out: [B,3,H,W] fp32; t: [B] int32 on the device. */
+ * (reference ViT.py:208-218).  x, out: [B,3,H,W] fp32; t: [B] int32 on the device, each in
+ * [0, total_steps).  The reference's nn.Embedding raises IndexError for a t outside the table
+ * (ViT.py:204); the Python class does the same before calling in.  The library cannot see device
+ * values from the host, so a raw caller's out-of-range t is clamped into the table by the kernel. */
 int ddc_forward(ddc_plan* plan, const float* x, const int32_t* t, int32_t batch, float* out, void* stream);
 
 /* ddc_forward for callers that cannot allocate device memory (no counterpart in the reference).
@@ -151,6 +158,16 @@ int ddc_launches_per_step(const ddc_plan* plan);
 int ddc_k_gemm(int32_t fmt, int32_t epi, int32_t M, int32_t N, int32_t K, const void* A, const void* W, const float* bias, void* out,
                int32_t ld_out, void* stream);
 
+/* Patch-embedding GEMM with the token assembly fused in (reference ViT.py:150,154,199-206) and the first LayerNorm
+ * (ViT.py:133):  x[b*L + l, :] = ap[b*L + l, :] * w_patch^T + posb[l, :] + time_tab[t_img[b], :]  (fp32), and
+ * xn = 16-bit LayerNorm(x; ln_g, ln_b, eps 1e-5).  ap: 16-bit [m_pad, Kp] from ddc_k_patchify (row b*L is the all-zero
+ * cls slot); w_patch: 16-bit [C, Kp]; posb: fp32 [L + 127, C] with row i = pos_embed[i % L] + (i % L == 0 ? cls_token :
+ * conv bias), i.e. the position table repeated so the 128 token rows of any tile are contiguous in it; time_tab: fp32
+ * [total_steps, C]; t_img: [batch] int32 on the device; x: fp32 [m_pad, C]; xn: 16-bit [batch*L, C]. */
+int ddc_k_embed(int32_t fmt, int32_t batch, int32_t L, int32_t C, int32_t Kp, int32_t total_steps, const void* ap,
+                const void* w_patch, const float* posb, const float* time_tab, const int32_t* t_img, const float* ln_g,
+                const float* ln_b, float* x, void* xn, void* stream);
+
 /* Residual GEMM with the following LayerNorm fused in (proj / fc2, reference ViT.py:136-137
  * then :133/:137/:212):  x[M, C] += A * W^T + bias  (fp32, in place; x allocated to m_pad
  * rows), and xn[M, C] = bf16(LayerNorm(x_new; ln_g, ln_b, eps 1e-5)).  A: bf16 [m_pad, K],
@@ -179,6 +196,10 @@ int ddc_k_patchify(int32_t fmt, const float* x, void* ap, int32_t batch, int32_t
  * by value.  y: fp32 [B*L, ldy] head output; x updated in place; x0_out / eps_out may be NULL. */
 int ddc_k_head_ddim(const float* y, int32_t ldy, float* x, int32_t batch, int32_t H, int32_t W, int32_t patch,
                     const ddc_step* host_step, float* x0_out, float* eps_out, void* stream);
+
+/* out[i] = (in[i] + add) * mul over n floats (16-byte aligned pointers; in == out allowed).  The samplers' return
+ * value is (x0 + 1) / 2 (reference ViT.py:237, ViT_draft2drawing.py:288): applied on the device before the copy back. */
+int ddc_k_affine(const float* in, float* out, size_t n, float add, float mul, void* stream);
 
 #ifdef __cplusplus
 }

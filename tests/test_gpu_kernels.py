@@ -67,6 +67,47 @@ def test_gemm_stream(lib, M, N, K, epi, fmt):
     assert torch.equal(out[M:], before[M:]), "rows beyond M were written"
 
 
+@pytest.mark.parametrize("B,L,C,P", [(3, 65, 384, 192), (2, 257, 256, 48), (1, 626, 384, 192), (5, 17, 64, 48),
+                                     (130, 65, 384, 192), (7, 65, 128, 48), (2, 100, 512, 192)])
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_embed_gemm(lib, B, L, C, P, fmt):
+    """Patch-embedding GEMM with the token assembly fused in (gemm2_kernel<R_EMBED>; ViT.py:150,154,199-206) and the
+    first LayerNorm: the all-zero cls slot of every image must come out as cls + pos[0] + time[t], the position rows
+    wrap around inside 128-row tiles (L = 65, 257, 626, 17, 100 are all coprime to 128), t differs per image."""
+    g = torch.Generator(device="cuda").manual_seed(B * 131 + L + C)
+    dev = "cuda"
+    T = 50
+    Kp = (P + 63) // 64 * 64
+    rnd = lambda *sh, s=1.0: torch.randn(*sh, device=dev, generator=g) * s
+    W = torch.zeros(C, Kp, device=dev)
+    W[:, :P] = rnd(C, P, s=0.07)
+    W = _op(W, fmt)
+    cls, pos, conv_b, time_tab = rnd(C, s=0.3), rnd(L, C, s=0.3), rnd(C, s=0.1), rnd(T, C, s=0.3)
+    ln_g, ln_b = 1 + rnd(C, s=0.1), rnd(C, s=0.1)
+    M = B * L
+    ap = torch.zeros(M, Kp, device=dev)
+    ap[:, :P] = rnd(M, P)
+    ap.view(B, L, Kp)[:, 0] = 0                                         # cls slots (ddc_k_patchify writes them as zeros)
+    ap = _pad_rows(_op(ap, fmt))
+    l_idx = torch.arange(L + 127, device=dev) % L
+    posb = (pos[l_idx] + torch.where((l_idx == 0)[:, None], cls[None], conv_b[None])).contiguous()
+    t_img = torch.randint(0, T, (B,), device=dev, generator=g, dtype=torch.int32)
+    x = torch.full((ap.shape[0], C), 5.0, device=dev)
+    xn = torch.full((M + 5, C), 3.0, device=dev, dtype=W.dtype)
+    _check(lib.ddc_k_embed(fmt, B, L, C, Kp, T, ap.data_ptr(), W.data_ptr(), posb.data_ptr(), time_tab.data_ptr(),
+                           t_img.data_ptr(), ln_g.data_ptr(), ln_b.data_ptr(), x.data_ptr(), xn.data_ptr(), _stream()))
+    torch.cuda.synchronize()
+    tok = (ap[:M].float() @ W.float().T).view(B, L, C)
+    tok = tok + torch.cat([(cls + pos[0])[None], pos[1:] + conv_b], dim=0)[None] + time_tab[t_img.long()][:, None]
+    x_ref = tok.reshape(M, C)
+    xn_ref = torch.nn.functional.layer_norm(x_ref, (C,), ln_g, ln_b, 1e-5)
+    assert (x[:M] - x_ref).abs().max().item() < 3e-3 * max(1.0, x_ref.abs().max().item())
+    cls_rows = x[:M].view(B, L, C)[:, 0]
+    assert (cls_rows - (cls + pos[0] + time_tab[t_img.long()])).abs().max().item() < 1e-5      # no GEMM term at all
+    assert (xn[:M].float() - xn_ref).abs().max().item() < (4e-3 if fmt else 2e-2) * max(1.0, xn_ref.abs().max().item())
+    assert bool((x[M:] == 5.0).all()) and bool((xn[M:].float() == 3.0).all()), "rows beyond M were written"
+
+
 @pytest.mark.parametrize("M,C,K", [(200, 64, 64), (130, 384, 384), (1000, 256, 256), (4097, 384, 384), (300, 128, 192),
                                    (66560 // 2, 384, 384), (515, 512, 512)])
 @pytest.mark.parametrize("fmt", [0, 1])

@@ -66,7 +66,7 @@ def test_hand_written_path_beats_stock_pytorch_on_the_same_gpu():
         "workload": f"S1 N={N} k={K} ({len(range(1999, 0, -K))} steps), one B200",
         "stock_torch_fp32_images_per_s": N / t_fp32,
         "stock_torch_bf16_autocast_images_per_s": N / t_bf16,
-        "ddim_cold_b200_bf16_images_per_s_incl_h2d": N / t_ours,
+        "ddim_cold_b200_images_per_s_incl_h2d": N / t_ours,
         "psnr_ours_vs_stock_fp32_db": psnr(img_ours.cpu().numpy(), img_fp32.cpu().numpy()),
         "torch": torch.__version__,
     }

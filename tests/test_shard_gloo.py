@@ -34,7 +34,14 @@ def _worker(rank, world, port, n, out_dir):
     torch.manual_seed(1234)                                  # same seed on every rank, like the reference's single process
     got = sample_sharded(_fake_local_sampler, n, (3, 8, 8))
     lo, hi = shard_bounds(n, world, rank)
-    torch.save({"all": got, "lo": lo, "hi": hi}, os.path.join(out_dir, f"r{rank}.pt"))
+    # the parallel-download path: every rank drops its slice into one host buffer shared through /dev/shm
+    from ddim_cold_b200.shard import SharedHostImages
+    shared = SharedHostImages(n, (3, 8, 8))
+    if hi > lo:
+        shared.put(lo, got[lo:hi])
+    host_all = shared.wait_all().clone()
+    shared.close()
+    torch.save({"all": got, "lo": lo, "hi": hi, "shared": host_all}, os.path.join(out_dir, f"r{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -51,6 +58,7 @@ def test_sharded_sampling_matches_single_process(tmp_path, n):
     r1 = torch.load(tmp_path / "r1.pt")
     assert torch.equal(r0["all"], want) and torch.equal(r1["all"], want)
     assert r0["lo"] == 0 and r0["hi"] == r1["lo"] and r1["hi"] == n
+    assert torch.equal(r0["shared"], want) and torch.equal(r1["shared"], want)
 
 
 def test_single_process_path_needs_no_process_group():
