@@ -17,6 +17,7 @@
 #include "gemm2.cuh"
 #include "block_tail.cuh"
 #include "attention_tc.cuh"
+#include "attention_fa.cuh"
 
 using namespace ddc;
 
@@ -237,6 +238,45 @@ static int att_pick_kc(int L) {
     return best;
 }
 
+// tcgen05 attention for long sequences (attention_fa.cuh) plus, when L = 128 n + r with a few remainder rows, the
+// CUDA-core kernel for those rows.  DDC_ATT_FA: 0 = never, 1 = L > 128 (default), 2 = every L.
+static bool attention_fa_wanted(int L, int C, int D) {
+    const int mode = env_int("DDC_ATT_FA", 1);
+    return (D == 32 || D == 64) && C % 64 == 0 && (mode == 2 || (mode == 1 && L > 128));
+}
+
+template <int D, bool F16>
+static int launch_att_fa(const bf16* qkv, bf16* out, int B, int L, int C, int heads, cudaStream_t st) {
+    static int attr_dev_mask = 0;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (!(attr_dev_mask & (1 << dev))) {
+        CK(cudaFuncSetAttribute(attention_fa_kernel<D, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM_BYTES));
+        attr_dev_mask |= (1 << dev);
+    }
+    FaParams p{};
+    p.L = L; p.C = C; p.n_hs = C / 64; p.n_items = B * p.n_hs;
+    p.n_hs_magic = p.n_hs > 1 ? static_cast<uint32_t>((1ull << 32) / static_cast<uint32_t>(p.n_hs)) + 1u : 0u;
+    fa_split_rows(L, &p.n_qt, &p.rows_main);
+    p.n_kc = (L + FA_KCH - 1) / FA_KCH;
+    p.scale_log2e = (1.0f / sqrtf(static_cast<float>(D))) * 1.44269504088896340736f;
+    if (p.rows_main < L && L > FA_ROWS_MAXJ * 32) return fail(DDC_E_INVALID, "attention: L=%d too long for the remainder-row kernel", L);
+    CUtensorMap tm;
+    TRY(make_tmap(&tm, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, 128));
+    int grid = num_sms();
+    if (grid > p.n_items) grid = p.n_items;
+    CK(launch_chain(attention_fa_kernel<D, F16>, dim3(grid), dim3(FA_THREADS), static_cast<size_t>(FA_SMEM_BYTES), st, 1, tm, out, p));
+    if (p.rows_main < L) {
+        const int n_tasks = B * heads * (L - p.rows_main);
+        int blocks = (n_tasks + 7) / 8;
+        if (blocks > 4 * num_sms()) blocks = 4 * num_sms();
+        CK(launch_chain(attention_rows_kernel<D, F16>, dim3(blocks), dim3(256), static_cast<size_t>(0), st, 1, qkv, out, B, L, C, heads,
+                        p.rows_main, p.scale_log2e));
+    }
+    CK(cudaGetLastError());
+    return DDC_OK;
+}
+
 template <int D, int KC, bool F16>
 static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads, cudaStream_t st) {
     static int attr_dev_mask = 0;
@@ -308,6 +348,10 @@ static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads
 static int run_attention(const bf16* qkv, bf16* out, int B, int L, int C, int heads, bool f16, cudaStream_t st) {
     if (heads <= 0 || C % heads != 0) return fail(DDC_E_INVALID, "attention: C=%d heads=%d", C, heads);
     const int D = C / heads;
+    if (attention_fa_wanted(L, C, D)) {
+        if (D == 32) return f16 ? launch_att_fa<32, true>(qkv, out, B, L, C, heads, st) : launch_att_fa<32, false>(qkv, out, B, L, C, heads, st);
+        return f16 ? launch_att_fa<64, true>(qkv, out, B, L, C, heads, st) : launch_att_fa<64, false>(qkv, out, B, L, C, heads, st);
+    }
     const int kc = att_pick_kc(L);
 #define ATT_CASE(DD, KK)                                                                \
     if (D == DD && kc == KK)                                                            \
@@ -554,7 +598,13 @@ extern "C" int ddc_launches_per_step(const ddc_plan* plan) {
     // patchify, embed GEMM, per block {qkv GEMM, attention, fused tail} or {qkv, attention, proj, fc1, fc2}, head GEMM,
     // head_ddim (the fused tail needs embed_dim % 128 == 0 and <= 384; other shapes use the separate kernels)
     const bool fused = block_tail_usable(plan->maxB * plan->L, plan->C, plan->bn_row);
-    return 2 + (fused ? 3 : 5) * plan->sh.depth + 2;
+    int att = 1;                     // the tcgen05 attention hands a few remainder rows to a second, CUDA-core launch
+    if (attention_fa_wanted(plan->L, plan->C, plan->C / plan->sh.heads)) {
+        int n_qt, rows_main;
+        fa_split_rows(plan->L, &n_qt, &rows_main);
+        if (rows_main < plan->L) att = 2;
+    }
+    return 2 + ((fused ? 2 : 4) + att) * plan->sh.depth + 2;
 }
 
 // ------------------------------------------------------------------------------- packing

@@ -166,7 +166,10 @@ def test_block_tail(lib, M, C, fmt):
 
 
 ATT_SHAPES = [(3, 65, 384, 12), (2, 257, 256, 4), (1, 626, 384, 12), (5, 17, 64, 2), (2, 33, 128, 2), (4, 16, 64, 1),
-              (300, 65, 384, 12), (3, 65, 128, 4), (2, 100, 256, 8), (2, 65, 256, 4)]
+              (300, 65, 384, 12), (3, 65, 128, 4), (2, 100, 256, 8), (2, 65, 256, 4),
+              # the tcgen05 kernel (L > 128): several items per CTA, odd tile counts, remainder rows, exact multiples
+              (40, 257, 256, 4), (30, 626, 384, 12), (3, 300, 128, 2), (2, 130, 128, 4), (2, 256, 64, 1), (1, 640, 64, 2),
+              (2, 129, 64, 2), (3, 385, 192, 3), (2, 200, 128, 4)]
 
 
 @pytest.mark.parametrize("B,L,Cdim,heads", ATT_SHAPES)
@@ -184,6 +187,24 @@ def test_attention(lib, B, L, Cdim, heads, fmt):
     ref = (p @ v).transpose(1, 2).reshape(B * L, Cdim)
     err = (out.float() - ref).abs().max().item()
     assert err < 2e-2 * max(1.0, ref.abs().max().item()), err
+
+
+@pytest.mark.parametrize("B,L,Cdim,heads", [(3, 65, 384, 12), (300, 65, 384, 12), (5, 17, 64, 2), (2, 100, 256, 8), (4, 16, 64, 1),
+                                            (2, 128, 128, 2), (9, 65, 128, 2)])
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_attention_flash_tcgen05_short_sequences(lib, B, L, Cdim, heads, fmt, monkeypatch):
+    """attention_fa.cuh forced onto short sequences too (DDC_ATT_FA=2): a single, partly filled query tile and a
+    single key chunk, masked keys, head pairs of 32 and single heads of 64."""
+    monkeypatch.setenv("DDC_ATT_FA", "2")
+    test_attention(lib, B, L, Cdim, heads, fmt)
+
+
+@pytest.mark.parametrize("B,L,Cdim,heads", [(2, 257, 256, 4), (1, 626, 384, 12)])
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_attention_legacy_long_sequence_kernel(lib, B, L, Cdim, heads, fmt, monkeypatch):
+    """The cp.async + mma.sync kernel that the tcgen05 one replaced for L > 128 stays selectable (DDC_ATT_FA=0)."""
+    monkeypatch.setenv("DDC_ATT_FA", "0")
+    test_attention(lib, B, L, Cdim, heads, fmt)
 
 
 @pytest.mark.parametrize("B,L,Cdim,heads", [(3, 65, 384, 12), (300, 65, 384, 12), (3, 65, 128, 4), (7, 65, 64, 2), (1, 65, 192, 6)])
