@@ -32,6 +32,13 @@ __device__ __forceinline__ float ex2_approx(float x) {
     return y;
 }
 
+// two exponentials per MUFU operation on a packed pair of IEEE halves; the result is the packed pair
+__device__ __forceinline__ uint32_t ex2_h2(uint32_t x) {
+    uint32_t y;
+    asm("ex2.approx.f16x2 %0, %1;" : "=r"(y) : "r"(x));
+    return y;
+}
+
 constexpr int ATT_MAX_WARPS = 8;
 constexpr int ATT_GROUP_WARPS = 8;     // group kernel: one warp per 16-query tile, each walking the G heads
 

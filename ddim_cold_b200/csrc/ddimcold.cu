@@ -255,9 +255,11 @@ static int launch_att_fa(const bf16* qkv, bf16* out, int B, int L, int C, int he
         attr_dev_mask |= (1 << dev);
     }
     FaParams p{};
-    p.L = L; p.C = C; p.n_hs = C / 64; p.n_items = B * p.n_hs;
-    p.n_hs_magic = p.n_hs > 1 ? static_cast<uint32_t>((1ull << 32) / static_cast<uint32_t>(p.n_hs)) + 1u : 0u;
+    p.L = L; p.C = C; p.n_hs = C / 64;
     fa_split_rows(L, &p.n_qt, &p.rows_main);
+    p.n_qi = D == 64 ? (p.n_qt + 1) / 2 : p.n_qt;       // head_dim 64: two query tiles per iteration; 32: two heads
+    p.n_items = B * p.n_hs * p.n_qi;
+    p.dbg = env_int("DDC_FA_DBG", 0);
     p.n_kc = (L + FA_KCH - 1) / FA_KCH;
     p.scale_log2e = (1.0f / sqrtf(static_cast<float>(D))) * 1.44269504088896340736f;
     if (p.rows_main < L && L > FA_ROWS_MAXJ * 32) return fail(DDC_E_INVALID, "attention: L=%d too long for the remainder-row kernel", L);
