@@ -9,10 +9,10 @@
 //                             and sum l in registers, P written as 16-bit rows of a K-major shared-memory tile
 //     O  += P V_c             tcgen05.mma with V as it lies in memory ([key][dim], i.e. an MN-major B operand); O lives
 //                             in TMEM across the chunks and is rescaled in place only when a row maximum jumps
-// Two softmax warpgroups run side by side on one tensor pipe: for head_dim 64 they take two consecutive query tiles
-// of the same head, for head_dim 32 the two heads of the pair on the same query tile (the head is a 64-byte offset
-// inside the 128-byte rows).  The exponentials are the bound (16 MUFU results per clock per SM); the tensor pipe
-// idles about three quarters of the time, which is why nothing here is double-buffered beyond the K/V ring.
+// Two tiles w = 0, 1 run side by side on one tensor pipe: for head_dim 64 two consecutive query tiles of the same
+// head, for head_dim 32 the two heads of the pair on the same query tile (the head is a 64-byte offset inside the
+// 128-byte rows).  Each tile has two softmax warpgroups, one per 64-key half of the chunk.  The exponentials are the
+// bound (16 MUFU results per clock per SM); the tensor pipe idles most of the time.
 //
 // A token count of the form 128 n + r with small r (S2: 257 = 2 * 128 + 1) would waste a whole 128-row tile on r
 // rows: those rows are left to attention_rows_kernel, one warp per (image, head, row) on the CUDA cores.
@@ -26,7 +26,7 @@
 
 namespace ddc {
 
-constexpr int FA_THREADS = 384;            // warp 0 TMEM + TMA, warp 1 MMA, warps 2-3 spare, warps 4-7 / 8-11 softmax
+constexpr int FA_THREADS = 640;            // warp 0 TMEM + TMA, warps 1-2 MMA (one per tile), warp 3 spare, warps 4-19 softmax
 constexpr int FA_KCH = 128;                // keys per chunk
 constexpr int FA_TILE = 128 * 128;         // bytes of a [128 rows x 128 B] tile
 // Shared memory = 13 tiles of 16 KB (two Q buffers -- head_dim 64: two query tiles each -- a K ring, a V ring, P) plus a
@@ -42,7 +42,7 @@ template <int D> struct FaCfg {
 };
 constexpr int FA_TMEM_W = 224;             // TMEM columns per warpgroup: S 128, O 64, row sums 32
 constexpr int FA_SIDE_MAX = 8;             // remainder rows handed to the CUDA-core kernel
-constexpr int FA_SMEM_BYTES = 1024 + 13 * FA_TILE + 2048 + 512;
+constexpr int FA_SMEM_BYTES = 1024 + 13 * FA_TILE + 2048 + 2048 + 512;
 
 struct FaParams {
     int L, C, n_items, n_hs;       // tokens, embed_dim, work items, head slots (64 columns) per image
@@ -82,7 +82,8 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tm,       // qkv [rows, 
     uint8_t* Vs = Ks + NK * FA_TILE;                    // NV tiles
     uint8_t* Ps = Vs + NV * FA_TILE;                    // per warpgroup: 2 K blocks of 64 keys
     uint8_t* Ones = Ps + 2 * 2 * FA_TILE;               // [16 rows x 128 B] of 1.0: the B operand of the row-sum MMAs
-    uint64_t* bars = reinterpret_cast<uint64_t*>(Ones + 2048);
+    float* xchg = reinterpret_cast<float*>(Ones + 2048);  // [tile][key half][128 rows] partial row maxima
+    uint64_t* bars = reinterpret_cast<uint64_t*>(Ones + 4096);
     uint64_t* q_full = bars;             // [2]
     uint64_t* q_empty = bars + 2;        // [2]
     uint64_t* k_full = bars + 4;         // [4]
@@ -98,14 +99,14 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tm,       // qkv [rows, 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         tma_prefetch_desc(&tm);
-        for (int i = 0; i < 4; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
-        for (int i = 0; i < 8; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+        for (int i = 0; i < 4; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 2); }        // released by both issuers
+        for (int i = 0; i < 8; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 2); }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&q_full[i], 1);
-            mbar_init(&q_empty[i], 1);
+            mbar_init(&q_empty[i], 2);
             mbar_init(&s_full[i], 1);
-            mbar_init(&s_free[i], 4);
-            mbar_init(&p_full[i], 4);
+            mbar_init(&s_free[i], 8);
+            mbar_init(&p_full[i], 8);
             mbar_init(&o_full[i], 1);
         }
         fence_barrier_init();
@@ -116,7 +117,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tm,       // qkv [rows, 
         tmem_relinquish<1>();
     }
     if (warp >= 4) {
-        for (int i = threadIdx.x - 128; i < 2048 / 4; i += 256) reinterpret_cast<uint32_t*>(Ones)[i] = F16 ? 0x3C003C00u : 0x3F803F80u;
+        for (int i = threadIdx.x - 128; i < 2048 / 4; i += 512) reinterpret_cast<uint32_t*>(Ones)[i] = F16 ? 0x3C003C00u : 0x3F803F80u;
         fence_proxy_async_smem();
     }
     tc_fence_before();
@@ -124,8 +125,8 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tm,       // qkv [rows, 
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();                         // qkv comes from the previous kernel
-    // 384 threads start with 168 registers each; a softmax thread holds a whole 128-key score row, so the control
-    // warpgroup hands its registers over (128 x 88 + 256 x 208 = 64512 <= 65536)
+    // 640 threads start with 96 registers each; the control warpgroup hands some over to the softmax threads, which hold
+    // 64 scores each (128 x 56 + 512 x 104 = 60416 <= 640 x 96: registers only move inside what the CTA got at launch)
     // (issued at the top of each role's own branch: code reachable from both settings is compiled for the smaller one)
 
     const int L = p.L, C = p.C;
@@ -138,7 +139,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tm,       // qkv [rows, 
     };
     auto tile_of = [&](int qi, int w) { return D == 64 ? 2 * qi + w : qi; };
 
-    if (warp < 4) asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
+    if (warp < 4) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
     if (warp == 0) {
         // ================================================================= TMA producer
         if (lane == 0) {
@@ -167,155 +168,154 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tm,       // qkv [rows, 
             }
         }
         __syncwarp();
-    } else if (warp == 1) {
-        // ================================================================= MMA issuer
-        // The two warpgroups are kept half a chunk apart on purpose: S of warpgroup 1 is issued only once warpgroup 0
-        // has pulled ITS S into registers, so one group's TMEM read (64 B/clk, ~1k cycles per chunk) runs under the
-        // other group's exponentials (MUFU, ~1k cycles per chunk) instead of both doing the same thing at once.
-        const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    } else if (warp == 1 || warp == 2) {
+        // ================================================================= MMA issuers: warp 1 for tile 0, warp 2 for tile 1
+        // One issuer per tile, each waiting only on its own tile's barriers: a single in-order issuer put eight blocking
+        // steps of 250-400 cycles each between "P of this tile is written" and "the next S of this tile is ready"
+        // (measured timeline), which was the chunk period.  The shared Q / K / V buffers are released by both (count 2).
+        const int w = warp - 1;
+        const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0) + static_cast<uint32_t>(w * FA_TMEM_W);
         const uint32_t idesc_o = umma_idesc_16bit(128, D, F16) | (1u << 16);      // B operand (V) is MN-major
         const uint32_t idesc_1 = umma_idesc_16bit(128, 16, F16);                  // row sums: P times 16 columns of ones
         const uint64_t od = umma_desc_sw128(smem_u32(Ones));
         const uint64_t qd0 = umma_desc_sw128(smem_u32(Qs));
         const uint64_t kd0 = umma_desc_sw128(smem_u32(Ks));
         const uint64_t vd0 = umma_desc_sw128(smem_u32(Vs));
-        const uint64_t pd = umma_desc_sw128(smem_u32(Ps));
+        const uint64_t pd = umma_desc_sw128(smem_u32(Ps)) + static_cast<uint64_t>(w * 2 * (FA_TILE >> 4));
         constexpr uint32_t kTileU = FA_TILE >> 4;
-        uint32_t q_it = 0, kv_it = 0, sfree_it[2] = {0, 0}, pfull_it[2] = {0, 0};
+        uint32_t q_it = 0, kv_it = 0, sfree_it = 0, pfull_it = 0;
+        // P*V of a chunk is issued one step late, after the NEXT chunk's Q K^T -- also across item boundaries, so that
+        // the first S of an item is under way while the softmax warps still work on the last chunk of the item before
+        bool pend = false, pend_act = false;
+        int pend_cc = 0;
+        uint32_t pend_it = 0;
+        // release a shared buffer: once this issuer's MMAs so far are complete, or at once if its tile has no work
+        auto release = [&](uint64_t* bar, bool act) {
+            if (elect_one()) {
+                if (act) umma_commit(bar);
+                else mbar_arrive(bar);
+            }
+            __syncwarp();
+        };
         for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++q_it) {
             int img, hs, qi;
             split(item, img, hs, qi);
-            const bool act1 = tile_of(qi, 1) < p.n_qt;
+            const bool act = tile_of(qi, w) < p.n_qt;
             const uint32_t qb = q_it & 1u;
             const uint64_t qd = qd0 + static_cast<uint64_t>(qb * QT * kTileU);
             mbar_wait(&q_full[qb], (q_it >> 1) & 1u);
             tc_fence_after();
-            // S_w(c) = Q_w K(c)^T into warpgroup w's S columns
-            auto issue_s = [&](int w, int c, uint32_t it) {
-                const int kvalid = L - c * FA_KCH < FA_KCH ? L - c * FA_KCH : FA_KCH;
-                const uint32_t idesc_s = umma_idesc_16bit(128, static_cast<uint32_t>((kvalid + 15) & ~15), F16);
-                const uint64_t kd = kd0 + static_cast<uint64_t>((it % NK) * kTileU);
-                mbar_wait(&s_free[w], (sfree_it[w] & 1) ^ 1);       // S of the previous chunk has been read out
-                ++sfree_it[w];
-                tc_fence_after();
-                if (elect_one()) {
-                    if (D == 64) {
-                        const uint64_t a = qd + static_cast<uint64_t>(w * kTileU);
-#pragma unroll
-                        for (int ks = 0; ks < 4; ++ks) umma_bf16_ss(tb + w * FA_TMEM_W, a + 2 * ks, kd + 2 * ks, idesc_s, ks);
-                    } else {            // head w of the pair: bytes [64 w, 64 w + 64) of every row
-#pragma unroll
-                        for (int ks = 0; ks < 2; ++ks)
-                            umma_bf16_ss(tb + w * FA_TMEM_W, qd + 4 * w + 2 * ks, kd + 4 * w + 2 * ks, idesc_s, ks);
-                    }
-                    umma_commit(&s_full[w]);
-                }
-                __syncwarp();
-            };
-            // O_w += P_w(cc) V(cc)
-            auto issue_pv = [&](int w, int cc, uint32_t it) {
-                const int kvalid = L - cc * FA_KCH < FA_KCH ? L - cc * FA_KCH : FA_KCH;
-                const int nks = (kvalid + 15) >> 4;
-                const uint64_t vd = vd0 + static_cast<uint64_t>((it % NV) * kTileU);
+            auto issue_pv = [&](bool act, int cc, uint32_t it) {          // O_w += P_w(cc) V(cc), row sums += P_w(cc) 1
                 mbar_wait(&v_full[it % NV], (it / NV) & 1u);
-                mbar_wait(&p_full[w], pfull_it[w] & 1);
-                ++pfull_it[w];
-                tc_fence_after();
-                if (elect_one()) {
-                    for (int ks = 0; ks < nks; ++ks) {
-                        const uint64_t a = pd + static_cast<uint64_t>(w * 2 * kTileU + (ks >> 2) * kTileU + (ks & 3) * 2);
-                        const uint64_t b = vd + static_cast<uint64_t>(ks * (2048 >> 4) + (D == 32 ? 4 * w : 0));
-                        umma_bf16_ss(tb + w * FA_TMEM_W + 128, a, b, idesc_o, (cc > 0 || ks > 0) ? 1u : 0u);
-                        umma_bf16_ss(tb + w * FA_TMEM_W + 128 + D, a, od, idesc_1, (cc > 0 || ks > 0) ? 1u : 0u);
+                if (act) {
+                    const int kvalid = L - cc * FA_KCH < FA_KCH ? L - cc * FA_KCH : FA_KCH;
+                    const int nks = (kvalid + 15) >> 4;
+                    const uint64_t vd = vd0 + static_cast<uint64_t>((it % NV) * kTileU);
+                    mbar_wait(&p_full[w], pfull_it & 1);
+                    ++pfull_it;
+                    tc_fence_after();
+                    if (elect_one()) {          // whole K blocks of 64 keys: the softmax warps zero-fill a started block
+                        const uint64_t vb = vd + static_cast<uint64_t>(D == 32 ? 4 * w : 0);
+                        umma_pv_kblock(tb + 128, tb + 128 + D, pd, vb, od, idesc_o, idesc_1, cc > 0 ? 1u : 0u);
+                        if (nks > 4) umma_pv_kblock(tb + 128, tb + 128 + D, pd + kTileU, vb + 4 * (2048 >> 4), od, idesc_o, idesc_1, 1u);
+                        umma_commit(&o_full[w]);
                     }
-                    umma_commit(&o_full[w]);
+                    __syncwarp();
                 }
-                __syncwarp();
-            };
-            auto release = [&](uint64_t* bar) {        // fires once every MMA issued so far has completed
-                if (elect_one()) umma_commit(bar);
-                __syncwarp();
+                release(&v_empty[it % NV], act);
             };
             for (int c = 0; c < p.n_kc; ++c, ++kv_it) {
                 FA_STAMP(0, kv_it, 0);
                 mbar_wait(&k_full[kv_it % NK], (kv_it / NK) & 1u);
                 tc_fence_after();
                 FA_STAMP(0, kv_it, 1);
-                issue_s(0, c, kv_it);
-                FA_STAMP(0, kv_it, 2);
-                if (!act1) release(&k_empty[kv_it % NK]);
-                if (c > 0) issue_pv(0, c - 1, kv_it - 1);
-                FA_STAMP(0, kv_it, 3);
-                if (act1) {
-                    mbar_wait(&s_free[0], (sfree_it[0] & 1) ^ 1);   // warpgroup 0 holds S_0(c) in registers (the stagger)
-                    FA_STAMP(0, kv_it, 4);
-                    issue_s(1, c, kv_it);
-                    FA_STAMP(0, kv_it, 5);
-                    release(&k_empty[kv_it % NK]);
-                    if (c > 0) issue_pv(1, c - 1, kv_it - 1);
-                    FA_STAMP(0, kv_it, 6);
+                if (act) {                                      // S_w(c) = Q_w K(c)^T
+                    const int kvalid = L - c * FA_KCH < FA_KCH ? L - c * FA_KCH : FA_KCH;
+                    const uint32_t idesc_s = umma_idesc_16bit(128, static_cast<uint32_t>((kvalid + 15) & ~15), F16);
+                    const uint64_t kd = kd0 + static_cast<uint64_t>((kv_it % NK) * kTileU);
+                    mbar_wait(&s_free[w], (sfree_it & 1) ^ 1);  // S of the previous chunk has been read out
+                    ++sfree_it;
+                    tc_fence_after();
+                    if (elect_one()) {
+                        if (D == 64) umma_kblock<1>(tb, qd + static_cast<uint64_t>(w * kTileU), kd, idesc_s, 0u);
+                        else umma_k32(tb, qd + 4 * w, kd + 4 * w, idesc_s);    // head w of the pair: bytes [64 w, +64) of every row
+                        umma_commit(&s_full[w]);
+                    }
+                    __syncwarp();
                 }
-                if (c == p.n_kc - 1) release(&q_empty[qb]);        // every S of this item is issued: Q may be replaced
-                if (c > 0) release(&v_empty[(kv_it - 1) % NV]);
+                FA_STAMP(0, kv_it, 2);
+                release(&k_empty[kv_it % NK], act);
+                if (c == p.n_kc - 1) release(&q_empty[qb], act);        // every S of this item is issued: Q may be replaced
+                if (pend) issue_pv(pend_act, pend_cc, pend_it);
+                pend = true; pend_act = act; pend_cc = c; pend_it = kv_it;
+                FA_STAMP(0, kv_it, 3);
             }
-            issue_pv(0, p.n_kc - 1, kv_it - 1);
-            if (act1) issue_pv(1, p.n_kc - 1, kv_it - 1);
-            release(&v_empty[(kv_it - 1) % NV]);
+            if (item + static_cast<int>(gridDim.x) >= p.n_items) issue_pv(pend_act, pend_cc, pend_it);      // last item: flush
         }
     } else if (warp >= 4) {
-        // ================================================================= softmax warpgroups (warps 4-7 and 8-11)
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
-        // A thread owns one query row.  It takes the row's 128 scores of the chunk from TMEM in one go (all four loads
-        // in flight, one wait), hands the S columns back at once so the next chunk's Q K^T runs under the exponentials,
-        // and never reads the scores again.  O stays in TMEM and accumulates there over the chunks (standard online
-        // softmax: when a row's maximum grows, the warp rescales its O rows -- and the row sums next to them -- in
-        // place).  The exponentials are the scarce resource (one MUFU unit per SM quarter): with IEEE-half operands two
-        // are computed per MUFU operation on a packed pair (ex2.approx.f16x2), whose result IS the packed P operand --
-        // no conversion after the exponential, and the pack / store of each 8 keys is interleaved with the next 8
-        // exponentials.  Row sums come from the tensor core (P times a block of ones), i.e. from the rounded P the
-        // numerator uses.
-        const int w = (warp - 4) >> 2;
+        // ================================================================= softmax warpgroups (warps 4-19)
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
+        // Four warpgroups: tile w = g / 2 (see the head comment), key half hf = g % 2 of every 128-key chunk.  A thread
+        // owns one query row and 64 of the chunk's keys: it takes those 64 scores from TMEM in one go, hands the S
+        // columns back at once (the pair's last reader releases them, so the next chunk's Q K^T runs under the
+        // exponentials) and never reads them again.  The two halves of a row exchange their maxima through shared
+        // memory (one named barrier per chunk).  O stays in TMEM and accumulates there over the chunks (online softmax:
+        // when a row's maximum grows, half 0 rescales the O rows in place, half 1 the row sums).  Row sums come from
+        // the tensor core (P times a block of ones), i.e. from the rounded P that the numerator uses.  The MUFU pipe
+        // (one unit per SM quarter, 128 exponentials per row and chunk) is the scarce resource; four softmax warps per
+        // quarter keep it fed while their neighbours wait, load, reduce or store.
+        const int g = (warp - 4) >> 2;
+        const int w = g >> 1, hf = g & 1;
         const int q = warp & 3;                         // a warp reads the TMEM lane quarter (warp id % 4)
         const int trow = q * 32 + lane;
         const uint32_t lane_taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(w * FA_TMEM_W);
-        uint8_t* Pw = Ps + static_cast<size_t>(w) * 2 * FA_TILE;
+        uint8_t* Pw = Ps + static_cast<size_t>(w) * 2 * FA_TILE + static_cast<size_t>(hf) * FA_TILE;     // this half's K block of 64 keys
+        float* my_max = xchg + (w * 2 + hf) * 128 + trow;
+        const float* other_max = xchg + (w * 2 + (hf ^ 1)) * 128 + trow;
         const float sc = p.scale_log2e;
         uint32_t sfull_it = 0, ofull_it = 0;
+        // The exponential phases of the two tiles take turns (named barriers 3 and 4 as a token): run at the same time
+        // they would only halve each other's MUFU rate, run alternately each overlaps the other tile's loads, waits,
+        // reductions and stores.  Tile 1 hands the token over once up front.
+        if (w == 1) asm volatile("bar.arrive 4, 512;" ::: "memory");
         for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
             int img, hs, qi;
             split(item, img, hs, qi);
             const int tile = tile_of(qi, w);
             if (tile >= p.n_qt) continue;
+            const bool both = tile_of(qi, 1) < p.n_qt;          // the other tile works on this item too
             const int row = tile * 128 + trow;
             float m = -INFINITY;
             for (int c = 0; c < p.n_kc; ++c) {
                 const int kvalid = L - c * FA_KCH < FA_KCH ? L - c * FA_KCH : FA_KCH;
+                const int hvalid = kvalid - 64 * hf < 64 ? kvalid - 64 * hf : 64;           // valid keys of this half (may be <= 0)
                 FA_STAMP(1 + w, sfull_it, 0);
                 mbar_wait(&s_full[w], sfull_it & 1);
                 FA_STAMP(1 + w, sfull_it, 1);
                 ++sfull_it;
                 tc_fence_after();
-                float v[128];
-                tmem_ld32_nowait(lane_taddr, v);
-                tmem_ld32_nowait(lane_taddr + 32, v + 32);
-                tmem_ld32_nowait(lane_taddr + 64, v + 64);
-                tmem_ld32_nowait(lane_taddr + 96, v + 96);
-                tmem_ld_wait(v);
+                float v[64];
+                tmem_ld32_nowait(lane_taddr + 64 * hf, v);
+                tmem_ld32_nowait(lane_taddr + 64 * hf + 32, v + 32);
+                tmem_ld_wait64(v);
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&s_free[w]);         // S is in registers: the next chunk's S may be computed
+                if (lane == 0) mbar_arrive(&s_free[w]);         // S is in registers (8 warps): the next chunk's S may be computed
                 FA_STAMP(1 + w, sfull_it - 1, 2);
-                if (kvalid < FA_KCH) {
+                if (hvalid < 64) {
 #pragma unroll
-                    for (int i = 0; i < 128; ++i) if (i >= kvalid) v[i] = -INFINITY;
+                    for (int i = 0; i < 64; ++i) if (i >= hvalid) v[i] = -INFINITY;
                 }
                 float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-                for (int i = 0; i < 128; i += 4) {
+                for (int i = 0; i < 64; i += 4) {
                     m4[0] = fmaxf(m4[0], v[i]); m4[1] = fmaxf(m4[1], v[i + 1]);
                     m4[2] = fmaxf(m4[2], v[i + 2]); m4[3] = fmaxf(m4[3], v[i + 3]);
                 }
-                const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * sc;      // scaled (log2) domain; scale > 0
+                float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+                *my_max = mx;
+                named_bar_sync(1 + w, 256);                     // both halves of tile w have published their maxima
+                mx = fmaxf(mx, *other_max) * sc;                // scaled (log2) domain; scale > 0; identical in both halves
                 float alpha = 1.f;
                 if (mx > m) { alpha = ex2_approx(m - mx); m = mx; }         // first chunk: 2^(-inf) = 0, unused
                 const bool rescale = c > 0 && __any_sync(0xffffffffu, alpha != 1.f);
@@ -324,9 +324,9 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tm,       // qkv [rows, 
                     mbar_wait(&o_full[w], ofull_it & 1);
                     ++ofull_it;
                     tc_fence_after();
-                    if (rescale) {
-#pragma unroll
-                        for (int h = 0; h < D / 32 + 1; ++h) {      // O, then the row sums in the 32 columns after it
+                    if (rescale) {                  // half 0: the O columns; half 1: the 32 columns holding the row sums
+                        const int h0 = hf == 0 ? 0 : D / 32, h1 = hf == 0 ? D / 32 : D / 32 + 1;
+                        for (int h = h0; h < h1; ++h) {
                             float ov[32];
                             tmem_ld32(lane_taddr + 128 + 32 * h, ov);
 #pragma unroll
@@ -336,32 +336,29 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tm,       // qkv [rows, 
                     }
                 }
                 FA_STAMP(1 + w, sfull_it - 1, 4);
-                const int nstore = (((kvalid + 7) >> 3) + 1) & ~1;      // 16-byte chunks of P the P*V MMAs can reach (16-key steps)
+                const int nstore = hvalid <= 0 ? 0 : 8;       // a started half is written whole: the P*V MMAs run over whole K blocks
                 const float nm = -m;
+                if (both && !(p.dbg & 8)) named_bar_sync(w == 0 ? 4 : 3, 512);      // my turn on the MUFU pipe
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
+                for (int j = 0; j < 8; ++j) {
                     if (j < nstore) {
-                        uint4 u;
-                        if (F16) {
-                            // packed pair: the argument is rounded to half (|x| <= a few tens where it matters, x <= 0)
-                            u.x = ex2_h2(pack2<true>(fmaf(v[8 * j], sc, nm), fmaf(v[8 * j + 1], sc, nm)));
-                            u.y = ex2_h2(pack2<true>(fmaf(v[8 * j + 2], sc, nm), fmaf(v[8 * j + 3], sc, nm)));
-                            u.z = ex2_h2(pack2<true>(fmaf(v[8 * j + 4], sc, nm), fmaf(v[8 * j + 5], sc, nm)));
-                            u.w = ex2_h2(pack2<true>(fmaf(v[8 * j + 6], sc, nm), fmaf(v[8 * j + 7], sc, nm)));
-                        } else {
-                            float e[8];
+                        float e[8];
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) e[i] = ex2_approx(fmaf(v[8 * j + i], sc, nm));
-                            u.x = pack2<false>(e[0], e[1]);
-                            u.y = pack2<false>(e[2], e[3]);
-                            u.z = pack2<false>(e[4], e[5]);
-                            u.w = pack2<false>(e[6], e[7]);
-                        }
-                        *reinterpret_cast<uint4*>(Pw + (j >> 3) * FA_TILE + slot_off(trow, j & 7)) = u;
+                        for (int i = 0; i < 8; ++i) e[i] = ex2_approx(fmaf(v[8 * j + i], sc, nm));      // masked keys: 2^(-inf) = 0
+                        uint4 u;
+                        u.x = pack2<F16>(e[0], e[1]);
+                        u.y = pack2<F16>(e[2], e[3]);
+                        u.z = pack2<F16>(e[4], e[5]);
+                        u.w = pack2<F16>(e[6], e[7]);
+                        *reinterpret_cast<uint4*>(Pw + slot_off(trow, j)) = u;
                     }
                 }
+                if (both && !(p.dbg & 8)) {
+                    if (w == 0) asm volatile("bar.arrive 3, 512;" ::: "memory");
+                    else asm volatile("bar.arrive 4, 512;" ::: "memory");
+                }
                 fence_proxy_async_smem();           // P -> visible to the tensor core
-                tc_fence_before();                  // and this warp's O rescale precedes the next P*V
+                tc_fence_before();                  // and this warp's rescale precedes the next P*V
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&p_full[w]);
                 FA_STAMP(1 + w, sfull_it - 1, 5);
@@ -372,21 +369,21 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tm,       // qkv [rows, 
             float lsum[32];
             tmem_ld32(lane_taddr + 128 + D, lsum);      // every one of the 16 sum columns holds the row sum
             const float inv = __frcp_rn(lsum[0]);
-            uint4* orow = reinterpret_cast<uint4*>(out + (static_cast<size_t>(img) * L + row) * C + hs * 64 + (D == 32 ? 32 * w : 0));
+            // half hf writes output columns [hf * D/2, +D/2) of the row
+            constexpr int HW = D / 2;
+            uint4* orow = reinterpret_cast<uint4*>(out + (static_cast<size_t>(img) * L + row) * C + hs * 64 + (D == 32 ? 32 * w : 0) + hf * HW);
+            float o[32];
+            if (D == 64) tmem_ld32(lane_taddr + 128 + 32 * hf, o);
+            else tmem_ld16(lane_taddr + 128 + 16 * hf, o);
+            if (row < p.rows_main) {
 #pragma unroll
-            for (int h = 0; h < D / 32; ++h) {
-                float o[32];
-                tmem_ld32(lane_taddr + 128 + 32 * h, o);
-                if (row < p.rows_main) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        uint4 u;
-                        u.x = pack2<F16>(o[8 * j] * inv, o[8 * j + 1] * inv);
-                        u.y = pack2<F16>(o[8 * j + 2] * inv, o[8 * j + 3] * inv);
-                        u.z = pack2<F16>(o[8 * j + 4] * inv, o[8 * j + 5] * inv);
-                        u.w = pack2<F16>(o[8 * j + 6] * inv, o[8 * j + 7] * inv);
-                        orow[4 * h + j] = u;
-                    }
+                for (int j = 0; j < HW / 8; ++j) {
+                    uint4 u;
+                    u.x = pack2<F16>(o[8 * j] * inv, o[8 * j + 1] * inv);
+                    u.y = pack2<F16>(o[8 * j + 2] * inv, o[8 * j + 3] * inv);
+                    u.z = pack2<F16>(o[8 * j + 4] * inv, o[8 * j + 5] * inv);
+                    u.w = pack2<F16>(o[8 * j + 6] * inv, o[8 * j + 7] * inv);
+                    orow[j] = u;
                 }
             }
             tc_fence_before();                      // the O reads precede the next item's first P*V (ordered through p_full)

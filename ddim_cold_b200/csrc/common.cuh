@@ -266,6 +266,42 @@ __device__ __forceinline__ void umma_kblock(uint32_t tmem_d, uint64_t adesc, uin
     if (CG == 2) DDC_UMMA_KBLOCK_ASM("2");
     else DDC_UMMA_KBLOCK_ASM("1");
 }
+// Attention P*V over one K block of 64 keys (four K = 16 steps), two accumulators per step: O (+)= P * V with V an
+// MN-major operand whose 16-key slices lie 2048 B apart (+128 descriptor units), and the row sums (+)= P * ones.  One asm
+// statement, uniform operands: the eight UTCHMMA issue back to back (a loop of single-MMA statements cost ~100 cycles
+// per instruction in descriptor arithmetic and register-to-uniform moves).
+__device__ __forceinline__ void umma_pv_kblock(uint32_t tmem_o, uint32_t tmem_sum, uint64_t pdesc, uint64_t vdesc, uint64_t onesdesc,
+                                               uint32_t idesc_o, uint32_t idesc_1, uint32_t accumulate_first) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 a1, b1;\n\t"
+        "setp.ne.b32 p, %7, 0;\n\t"
+        "setp.eq.b32 q, 0, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %2, %3, %5, p;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%1], %2, %4, %6, p;\n\t"
+        "add.u64 a1, %2, 2;\n\tadd.u64 b1, %3, 128;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %5, q;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%1], a1, %4, %6, q;\n\t"
+        "add.u64 a1, %2, 4;\n\tadd.u64 b1, %3, 256;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %5, q;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%1], a1, %4, %6, q;\n\t"
+        "add.u64 a1, %2, 6;\n\tadd.u64 b1, %3, 384;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %5, q;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%1], a1, %4, %6, q;\n\t}"
+        ::"r"(tmem_o), "r"(tmem_sum), "l"(pdesc), "l"(vdesc), "l"(onesdesc), "r"(idesc_o), "r"(idesc_1), "r"(accumulate_first)
+        : "memory");
+}
+// Q K^T over a head of 32 dims: two K = 16 steps, fresh accumulator
+__device__ __forceinline__ void umma_k32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 a1, b1;\n\t"
+        "setp.ne.b32 p, 0, 0;\n\t"
+        "setp.eq.b32 q, 0, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "add.u64 a1, %1, 2;\n\tadd.u64 b1, %2, 2;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, q;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc)
+        : "memory");
+}
 // True in exactly one lane of the (fully active) warp; ptxas recognises the pattern and needs no
 // per-instruction leader election for the single-thread tcgen05 / TMA instructions that follow.
 __device__ __forceinline__ bool elect_one() {
@@ -347,6 +383,12 @@ __device__ __forceinline__ void tmem_ld_wait(float* v) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
     for (int i = 0; i < 128; i += 8)
+        asm volatile("" : "+f"(v[i]), "+f"(v[i + 1]), "+f"(v[i + 2]), "+f"(v[i + 3]), "+f"(v[i + 4]), "+f"(v[i + 5]), "+f"(v[i + 6]), "+f"(v[i + 7]));
+}
+__device__ __forceinline__ void tmem_ld_wait64(float* v) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 64; i += 8)
         asm volatile("" : "+f"(v[i]), "+f"(v[i + 1]), "+f"(v[i + 2]), "+f"(v[i + 3]), "+f"(v[i + 4]), "+f"(v[i + 5]), "+f"(v[i + 6]), "+f"(v[i + 7]));
 }
 // registers -> TMEM: this warp's 32 lanes x 32 consecutive fp32 columns

@@ -239,10 +239,13 @@ static int att_pick_kc(int L) {
 }
 
 // tcgen05 attention for long sequences (attention_fa.cuh) plus, when L = 128 n + r with a few remainder rows, the
-// CUDA-core kernel for those rows.  DDC_ATT_FA: 0 = never, 1 = L > 128 (default), 2 = every L.
+// CUDA-core kernel for those rows.  DDC_ATT_FA: 0 = never; 1 (default) = where it measures at least as fast as the
+// mma.sync kernel: head_dim 32 and L > 128 (S3: 617 vs 602 us per launch; S2, head_dim 64, is 386 vs 330 us and stays
+// on the mma.sync kernel); 2 = every shape; 3 = every L > 128.
 static bool attention_fa_wanted(int L, int C, int D) {
     const int mode = env_int("DDC_ATT_FA", 1);
-    return (D == 32 || D == 64) && C % 64 == 0 && (mode == 2 || (mode == 1 && L > 128));
+    if (!((D == 32 || D == 64) && C % 64 == 0)) return false;
+    return mode == 2 || (mode == 3 && L > 128) || (mode == 1 && L > 128 && D == 32);
 }
 
 template <int D, bool F16>

@@ -199,6 +199,17 @@ def test_attention_flash_tcgen05_short_sequences(lib, B, L, Cdim, heads, fmt, mo
     test_attention(lib, B, L, Cdim, heads, fmt)
 
 
+@pytest.mark.parametrize("B,L,Cdim,heads", [(2, 257, 256, 4), (40, 257, 256, 4), (2, 256, 64, 1), (1, 640, 64, 1), (2, 129, 64, 1),
+                                            (3, 385, 192, 3), (3, 300, 128, 2)])
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_attention_flash_tcgen05_head_dim_64(lib, B, L, Cdim, heads, fmt, monkeypatch):
+    """Long sequences with head_dim 64 take the mma.sync kernel by default (it measures faster there); DDC_ATT_FA=3
+    sends them through attention_fa.cuh: two query tiles per item, an idle second tile when their number is odd,
+    remainder rows on the CUDA cores (257 = 2 * 128 + 1)."""
+    monkeypatch.setenv("DDC_ATT_FA", "3")
+    test_attention(lib, B, L, Cdim, heads, fmt)
+
+
 @pytest.mark.parametrize("B,L,Cdim,heads", [(2, 257, 256, 4), (1, 626, 384, 12)])
 @pytest.mark.parametrize("fmt", [0, 1])
 def test_attention_legacy_long_sequence_kernel(lib, B, L, Cdim, heads, fmt, monkeypatch):
