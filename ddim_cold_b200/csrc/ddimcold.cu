@@ -18,6 +18,7 @@
 #include "block_tail.cuh"
 #include "attention_tc.cuh"
 #include "attention_fa.cuh"
+#include "fp32_path.cuh"
 
 using namespace ddc;
 
@@ -391,6 +392,11 @@ struct ddc_plan {
     int bn_qkv, bn_fc1, bn_row, bn_head;
     bool packed;
     bool f16;       // 16-bit operand format: false = bfloat16 (default), true = IEEE half
+    bool f32;       // fp32 mode: every contraction in fp32 on the CUDA cores (fp32_path.cuh); overrides f16
+    // fp32 mode reads the weight matrices where the caller keeps them (state_dict tensors given to ddc_pack_weights)
+    const float* w32_patch;
+    const float* w32_head;
+    std::vector<const float*> w32_qkv, w32_proj, w32_fc1, w32_fc2;
     // weight arena
     bf16* w_patch;
     float* posb;
@@ -537,6 +543,7 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
     pl->device = device;
     pl->packed = false;
     pl->f16 = false;
+    pl->f32 = false;
     pl->gexec = nullptr;
     pl->gkey = GraphKey{0, nullptr, nullptr, nullptr, nullptr};
     pl->fixed_view_cap = 0;
@@ -586,9 +593,10 @@ extern "C" int ddc_plan_destroy(ddc_plan* plan) {
 
 extern "C" int ddc_plan_set_operand_format(ddc_plan* plan, int32_t fmt) {
     if (plan == nullptr) return fail(DDC_E_INVALID, "plan is NULL");
-    if (fmt != 0 && fmt != 1) return fail(DDC_E_INVALID, "operand format %d (0 = bf16, 1 = fp16)", fmt);
-    if (plan->f16 != (fmt == 1)) {
+    if (fmt < 0 || fmt > 2) return fail(DDC_E_INVALID, "operand format %d (0 = bf16, 1 = fp16, 2 = fp32)", fmt);
+    if (plan->f16 != (fmt == 1) || plan->f32 != (fmt == 2)) {
         plan->f16 = (fmt == 1);
+        plan->f32 = (fmt == 2);
         plan->packed = false;            // packed weights are in the old format
         if (plan->gexec) {
             cudaGraphExecDestroy(plan->gexec);
@@ -598,10 +606,18 @@ extern "C" int ddc_plan_set_operand_format(ddc_plan* plan, int32_t fmt) {
     return DDC_OK;
 }
 
+static int f32_max_batch(const ddc_plan* pl);
+
+extern "C" int ddc_plan_max_batch(const ddc_plan* plan) {
+    if (plan == nullptr) return 0;
+    return plan->f32 ? f32_max_batch(plan) : plan->maxB;
+}
+
 extern "C" int ddc_launches_per_step(const ddc_plan* plan) {
     if (plan == nullptr) return 0;
     // patchify, embed GEMM, per block {qkv GEMM, attention, fused tail} or {qkv, attention, proj, fc1, fc2}, head GEMM,
     // head_ddim (the fused tail needs embed_dim % 128 == 0 and <= 384; other shapes use the separate kernels)
+    if (plan->f32) return 2 + 7 * plan->sh.depth + 3;      // patchify, embed, depth x {LN, qkv, attention, proj, LN, fc1, fc2}, LN, head, head_ddim
     const bool fused = block_tail_usable(plan->maxB * plan->L, plan->C, plan->bn_row);
     int att = 1;                     // the tcgen05 attention hands a few remainder rows to a second, CUDA-core launch
     if (attention_fa_wanted(plan->L, plan->C, plan->C / plan->sh.heads)) {
@@ -623,12 +639,21 @@ extern "C" int ddc_pack_weights(ddc_plan* pl, const float* const* t, int32_t n_t
     CK(cudaSetDevice(pl->device));
     const int C = pl->C, L = pl->L, P = pl->P;
     auto pack = [&](const float* src, bf16* dst, int rows, int cols, int cols_pad) {
+        if (pl->f32) return;                          // fp32 mode multiplies by the caller's fp32 matrices directly
         if (pl->f16) pack_16bit_kernel<true><<<296, 256, 0, st>>>(src, dst, rows, cols, cols_pad);
         else pack_16bit_kernel<false><<<296, 256, 0, st>>>(src, dst, rows, cols, cols_pad);
     };
     auto copy = [&](const float* src, float* dst, size_t n) { copy_f32_kernel<<<148, 256, 0, st>>>(src, dst, n); };
     const float* cls = t[0];
     const float* pos = t[1];
+    pl->w32_patch = t[2];
+    pl->w32_head = t[5 + 12 * pl->sh.depth + 2];
+    pl->w32_qkv.assign(pl->sh.depth, nullptr); pl->w32_proj.assign(pl->sh.depth, nullptr);
+    pl->w32_fc1.assign(pl->sh.depth, nullptr); pl->w32_fc2.assign(pl->sh.depth, nullptr);
+    for (int i = 0; i < pl->sh.depth; ++i) {
+        const float* const* b = t + 5 + 12 * i;
+        pl->w32_qkv[i] = b[2]; pl->w32_proj[i] = b[4]; pl->w32_fc1[i] = b[8]; pl->w32_fc2[i] = b[10];
+    }
     pack(t[2], pl->w_patch, C, P, pl->Kp);
     pack_posb_kernel<<<148, 256, 0, st>>>(pos, cls, t[3], pl->posb, L, C, L + 127);
     copy(t[4], pl->time_tab, static_cast<size_t>(pl->sh.total_steps) * C);
@@ -706,11 +731,97 @@ static int ensure_store_maps(ddc_plan* pl, int B) {
     return DDC_OK;
 }
 
+// ------------------------------------------------------------------------------- fp32 mode
+// The fp32 activations (LayerNorm output, qkv, attention output, MLP hidden, im2col) overlay the region of the work arena
+// that the 16-bit path uses for its 16-bit activations; X, Y, the step table and the counter are shared.  fp32 rows are
+// twice as wide, so a plan created for max_batch images serves about half as many in this mode.
+struct F32View {
+    float *XN, *QKV, *O, *H, *Ap;
+};
+static bool f32_layout(const ddc_plan* pl, int B, F32View* v) {
+    const size_t rows = static_cast<size_t>(B) * pl->L, C = pl->C, P = pl->P;
+    Carver k{reinterpret_cast<char*>(pl->QKV), 0};
+    F32View t;
+    t.XN = k.take<float>(rows * C);
+    t.QKV = k.take<float>(rows * 3 * C);
+    t.O = k.take<float>(rows * C);
+    t.H = k.take<float>(rows * C);
+    t.Ap = k.take<float>(rows * P);
+    if (v != nullptr) *v = t;
+    return k.off <= static_cast<size_t>(reinterpret_cast<char*>(pl->Y) - reinterpret_cast<char*>(pl->QKV));
+}
+static int f32_max_batch(const ddc_plan* pl) {
+    int b = pl->maxB;
+    while (b > 0 && !f32_layout(pl, b, nullptr)) --b;
+    return b;
+}
+
+template <int EPI>
+static int launch_sgemm(const float* A, const float* Wt, const float* bias, float* out, int M, int N, int K, const SgemmEmbed& e,
+                        cudaStream_t st) {
+    if (K % 8 != 0) return fail(DDC_E_INVALID, "fp32 GEMM: K=%d must be a multiple of 8", K);
+    dim3 grid((N + 127) / 128, (M + 127) / 128);
+    sgemm_f32_kernel<EPI><<<grid, 256, 0, st>>>(A, Wt, bias, out, M, N, K, e);
+    CK(cudaGetLastError());
+    return DDC_OK;
+}
+
+static int enqueue_predictor_f32(ddc_plan* pl, const float* x, int B, const int* t_img, bool use_step_ctr, cudaStream_t st, Prof* prof) {
+    const ddc_shape& s = pl->sh;
+    const int C = pl->C, L = pl->L, P = pl->P, M = B * L;
+    F32View v;
+    if (!f32_layout(pl, B, &v)) return fail(DDC_E_INVALID, "fp32 mode: batch %d does not fit this plan (at most %d)", B, f32_max_batch(pl));
+    const int D = C / s.heads;
+    static int attr_dev_mask = 0;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (!(attr_dev_mask & (1 << dev))) {
+        CK(cudaFuncSetAttribute(attention_f32_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CK(cudaFuncSetAttribute(attention_f32_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_dev_mask |= (1 << dev);
+    }
+    const size_t att_smem = attention_f32_smem(L, D);
+    if (att_smem > 227 * 1024) return fail(DDC_E_INVALID, "fp32 attention: L=%d needs %zu B of shared memory", L, att_smem);
+    SgemmEmbed none{};
+    patchify_f32_kernel<<<dim3(s.img_h / s.patch, B), 256, 0, st>>>(x, v.Ap, s.img_h, s.img_w, s.patch, L, P, use_step_ctr ? pl->ctr : nullptr);
+    CK(cudaGetLastError());
+    MARK(KC_PATCHIFY);
+    SgemmEmbed e{};
+    e.posb = pl->posb; e.time_tab = pl->time_tab; e.t_img = t_img; e.tbl = pl->tbl; e.cur = pl->ctr; e.L = L; e.T = s.total_steps;
+    TRY(launch_sgemm<F_EMBED>(v.Ap, pl->w32_patch, nullptr, pl->X, M, C, P, e, st));
+    MARK(KC_EMBED);
+    const int ln_blocks = (M + 7) / 8;
+    for (int i = 0; i < s.depth; ++i) {
+        const LayerW& l = pl->layers[i];
+        layernorm_f32_kernel<<<ln_blocks, 256, 0, st>>>(pl->X, l.ln1_g, l.ln1_b, v.XN, M, C, 1e-5f);
+        TRY(launch_sgemm<F_BIAS>(v.XN, pl->w32_qkv[i], l.b_qkv, v.QKV, M, 3 * C, C, none, st));
+        MARK(KC_QKV);
+        const float scale = 1.0f / sqrtf(static_cast<float>(D));
+        if (D == 32) attention_f32_kernel<32><<<dim3(s.heads, B), 256, att_smem, st>>>(v.QKV, v.O, L, C, scale);
+        else attention_f32_kernel<64><<<dim3(s.heads, B), 256, att_smem, st>>>(v.QKV, v.O, L, C, scale);
+        CK(cudaGetLastError());
+        MARK(KC_ATTN);
+        TRY(launch_sgemm<F_RESID>(v.O, pl->w32_proj[i], l.b_proj, pl->X, M, C, C, none, st));
+        MARK(KC_PROJ);
+        layernorm_f32_kernel<<<ln_blocks, 256, 0, st>>>(pl->X, l.ln2_g, l.ln2_b, v.XN, M, C, 1e-5f);
+        TRY(launch_sgemm<F_GELU>(v.XN, pl->w32_fc1[i], l.b_fc1, v.H, M, C, C, none, st));
+        MARK(KC_FC1);
+        TRY(launch_sgemm<F_RESID>(v.H, pl->w32_fc2[i], l.b_fc2, pl->X, M, C, C, none, st));
+        MARK(KC_FC2);
+    }
+    layernorm_f32_kernel<<<ln_blocks, 256, 0, st>>>(pl->X, pl->lnf_g, pl->lnf_b, v.XN, M, C, 1e-5f);
+    TRY(launch_sgemm<F_BIAS>(v.XN, pl->w32_head, pl->b_head, pl->Y, M, P, C, none, st));
+    CK(cudaGetLastError());
+    MARK(KC_HEAD);
+    return DDC_OK;
+}
+
 // Enqueues: patchify -> patch-embed GEMM (+cls/pos/time, emits LN1(0)) -> depth x [qkv GEMM,
 // attention, proj GEMM (+residual, emits LN2), fc1 GEMM (+GELU), fc2 GEMM (+residual, emits the
 // next LayerNorm)] -> head GEMM.  Leaves the head output in pl->Y.
 static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_img, bool use_step_ctr, cudaStream_t st,
                              Prof* prof = nullptr) {
+    if (pl->f32) return enqueue_predictor_f32(pl, x, B, t_img, use_step_ctr, st, prof);
     const ddc_shape& s = pl->sh;
     const int C = pl->C, L = pl->L, M = B * L;
     TRY(ensure_store_maps(pl, B));
@@ -778,6 +889,9 @@ static int check_call(ddc_plan* pl, int batch) {
     if (pl == nullptr) return fail(DDC_E_INVALID, "plan is NULL");
     if (!pl->packed) return fail(DDC_E_STATE, "ddc_pack_weights has not been called on this plan");
     if (batch <= 0 || batch > pl->maxB) return fail(DDC_E_INVALID, "batch %d outside 1..%d", batch, pl->maxB);
+    if (pl->f32 && !f32_layout(pl, batch, nullptr))
+        return fail(DDC_E_INVALID, "fp32 mode: batch %d does not fit this plan (fp32 activations are twice as wide: at most %d)", batch,
+                    f32_max_batch(pl));
     return DDC_OK;
 }
 
@@ -849,6 +963,7 @@ extern "C" int ddc_forward_fixed_scratch(ddc_plan* pl, const float* x, const int
     if (!pl->packed) return fail(DDC_E_STATE, "ddc_pack_weights has not been called on this plan");
     if (x == nullptr || t == nullptr || out == nullptr) return fail(DDC_E_INVALID, "NULL tensor");
     if (batch <= 0) return fail(DDC_E_INVALID, "batch %d", batch);
+    if (pl->f32) return fail(DDC_E_STATE, "ddc_forward_fixed_scratch serves the 16-bit operand formats only (the plan is in fp32 mode)");
     const size_t need = fixed_scratch_layout(pl, batch, nullptr, nullptr);
     if (need > DDC_FIXED_SCRATCH_BYTES) {
         int fit = batch;

@@ -81,11 +81,19 @@ int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_t device, v
                     void* work_arena, size_t work_bytes, ddc_plan** out);
 int ddc_plan_destroy(ddc_plan* plan);
 
-/* Choose the 16-bit format of every tensor-core operand (weights and activations): 0 =
- * bfloat16 (default), 1 = IEEE half.  Both run at the same tensor-core rate with fp32
- * accumulation; half carries three more mantissa bits (the reference itself computes in fp32,
- * ViT.py has no autocast on this path).  Must be followed by ddc_pack_weights. */
+/* Choose the arithmetic format: 0 = bfloat16 tensor-core operands (the C default), 1 = IEEE half
+ * tensor-core operands (what the Python class selects by default: same rate, three more mantissa
+ * bits, meets the 1e-2 per-step eps bound that bfloat16 misses), 2 = fp32 mode: every contraction
+ * in fp32 on the CUDA cores (the reference itself computes in fp32, ViT.py:208-218 has no autocast
+ * on this path; per-step eps within 1e-4; a precision mode at a few per cent of the 16-bit
+ * throughput).  Formats 0 and 1 accumulate in fp32.  Must be followed by ddc_pack_weights.  In fp32
+ * mode ddc_pack_weights copies nothing but the small fp32 tables: the weight matrices are read from
+ * the state_dict tensors it was given, which must stay alive and unchanged; and the fp32
+ * activations are twice as wide, so the plan serves about half of max_batch (ddc_plan_max_batch). */
 int ddc_plan_set_operand_format(ddc_plan* plan, int32_t fmt);
+
+/* Largest batch the plan accepts in its current format (max_batch for the 16-bit formats). */
+int ddc_plan_max_batch(const ddc_plan* plan);
 
 /* Pack an fp32 state dict into the plan's weight arena (bf16 K-major GEMM operands, folded
  * cls/pos/conv-bias rows, fp32 time table).  `tensors` is a HOST array of `n_tensors` device

@@ -253,3 +253,61 @@ def test_s3_forward_and_sampler_vs_reference_fixture(golden):
     p = psnr(img, g["samp500_img"])
     print(f"s3: free-running sampler k=500 PSNR vs reference = {p:.1f} dB")
     assert p > PSNR_MIN
+
+
+EPS_TOL_FP32 = 1e-4     # north_star: per-step eps max-abs in fp32 mode
+
+
+@pytest.mark.parametrize("tag,seed", [("s1", 0), ("s2", 1)])
+def test_fp32_mode_teacher_forced_eps(golden, tag, seed):
+    """operand_format = "fp32" (every contraction in fp32 on the CUDA cores): per-step x0 and derived eps against the
+    reference's own values at the recorded x_t within 1e-4, and the free-running sampler image."""
+    from oracle import ddim_oracle as O
+    sh = {"s1": O.S1, "s2": O.S2}[tag]
+    g = golden(tag)
+    sd = O.synth_state_dict(sh, seed=seed, rich=True)
+    m = build(sh, sd, fmt="fp32")
+    worst_x0 = worst_eps = 0.0
+    for j, t in enumerate(g["tap_t"]):
+        x_t = g["tap_x_t"][j]
+        x0 = torch.clamp(m(torch.from_numpy(x_t).cuda(), torch.tensor([int(t)]).cuda()), -1, 1).cpu().numpy()
+        eps, _ = O.ddim_update(x_t, x0, int(t), 100)
+        worst_x0 = max(worst_x0, float(np.abs(x0 - g["tap_x0"][j]).max()))
+        worst_eps = max(worst_eps, float(np.abs(eps - g["tap_eps"][j]).max()))
+    print(f"{tag} fp32 mode: teacher-forced max|x0 err|={worst_x0:.3e} max|eps err|={worst_eps:.3e}")
+    assert worst_x0 < EPS_TOL_FP32 and worst_eps < EPS_TOL_FP32, (worst_x0, worst_eps)
+    img = m.sampler("cuda", 100, 2, noise=torch.from_numpy(g["xT"])).numpy()
+    err = float(np.abs(img - g["samp100_img"]).max())
+    print(f"{tag} fp32 mode: free-running sampler k=100 max|image err| = {err:.3e}, PSNR {psnr(img, g['samp100_img']):.1f} dB")
+    assert err < 1e-3 and psnr(img, g["samp100_img"]) > 80.0
+
+
+def test_fp32_mode_tiny_api_and_hot_weights(tiny):
+    """fp32 mode on the fixture-sized model whose weights are scaled x4 (53 % of the pixels hit the clamp, softmax and GELU
+    see large arguments): forward with per-image t, sampler, cold sampler, and switching the same model between formats."""
+    g, sd, m16 = tiny
+    from oracle import ddim_oracle as O
+    m = build(O.TINY, sd, fmt="fp32")
+    y = m(torch.from_numpy(g["fwd_x"]).cuda(), torch.from_numpy(g["fwd_t"]).cuda()).cpu().numpy()
+    assert np.abs(y - g["fwd_y"]).max() < 2e-4 * max(1.0, np.abs(g["fwd_y"]).max())
+    for k in (100, 2000):
+        img = m.sampler("cuda", k, 3, noise=torch.from_numpy(g[f"samp{k}_xT"])).numpy()
+        assert np.abs(img - g[f"samp{k}_img"]).max() < 2e-3, k          # free-running over up to 20 steps, hot weights
+    z = torch.from_numpy(g["cold_z"])
+    assert np.abs(m.cold_sampler("cuda", 10, 4, z=z).numpy() - g["cold_img"]).max() < 2e-3
+    a = m.sampler("cuda", 500, 3, noise=torch.from_numpy(g["samp500_xT"]))
+    m.operand_format = "fp16"
+    b = m.sampler("cuda", 500, 3, noise=torch.from_numpy(g["samp500_xT"]))
+    m.operand_format = "fp32"
+    c = m.sampler("cuda", 500, 3, noise=torch.from_numpy(g["samp500_xT"]))
+    assert torch.equal(a, c) and psnr(a.numpy(), b.numpy()) > PSNR_MIN and not torch.equal(a, b)
+
+
+def test_fp32_mode_s3_forward(golden):
+    from oracle import ddim_oracle as O
+    g = golden("s3")
+    m = build(O.S3, O.synth_state_dict(O.S3, seed=2, rich=True), fmt="fp32")
+    y = m(torch.from_numpy(g["fwd_x"]).cuda(), torch.from_numpy(g["fwd_t"]).cuda()).cpu().numpy()
+    err = float(np.abs(y - g["fwd_y"]).max())
+    print(f"s3 fp32 mode forward: max|y err| = {err:.3e}")
+    assert err < EPS_TOL_FP32
