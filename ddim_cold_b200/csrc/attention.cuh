@@ -9,11 +9,8 @@
 // operands, fp32 accumulation).
 //
 // Two launch shapes:
-//   * attention_group_kernel: one CTA per (image, group of G heads with G*D = 128).  Q, K, V
-//     column slices of 256 B per token are staged with cp.async (full-line reads), every
-//     (head, q-tile) pair is a warp task, and the output tile is staged back through the Q
-//     buffer so that O rows leave as 256-byte segments.  Used when one image's slice fits
-//     comfortably (L <= 128: S1, 65 tokens).
+//   * attention_stream_kernel: persistent CTAs, work item = (image, 64 qkv columns), Q / K / V tiles by TMA into a
+//     double-buffered stage, every (head, q-tile) pair a warp task.  Used for short sequences (L <= 128: S1, 65 tokens).
 //   * attention_head_kernel: one CTA per (image, head), K/V in shared memory, Q fragments read
 //     directly from global.  Used for long sequences (S2 257 tokens, S3 626 tokens).
 //
@@ -161,82 +158,6 @@ __device__ __forceinline__ void attend_qtile(const uint32_t (&qa)[D / 16][4], co
     const float i0 = __frcp_rn(lsum[0]), i1 = __frcp_rn(lsum[2]);     // sums are >= 1 (the row maximum contributes 1)
 #pragma unroll
     for (int i = 0; i < DT; ++i) { o[i][0] *= i0; o[i][1] *= i0; o[i][2] *= i1; o[i][3] *= i1; }
-}
-
-// ---------------------------------------------------------------------------- one CTA per (image, G heads)
-// Q, K and V column slices (G heads = 128 qkv columns) arrive as six [lk_pad x 64] TMA boxes in the 128-byte
-// swizzle behind one mbarrier -- no per-thread copy loop.  Rows [L, lk_pad) of a box belong to the next image
-// (or are zero-filled past the end): finite, and masked as keys.
-inline size_t att_group_smem_bytes(int L, int KC) {
-    const int lk = (L + KC - 1) / KC * KC;
-    return 1024 + static_cast<size_t>(6) * lk * 128 + 64;
-}
-
-template <int D, int KC, bool F16>
-__global__ void __launch_bounds__(ATT_GROUP_WARPS * 32, 2)
-attention_group_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ out, int L, int C,
-                       float scale_log2e) {
-    extern __shared__ uint8_t att_raw[];
-    pdl_launch_dependents();
-    pdl_wait();        // qkv comes from the previous kernel; nothing worth doing before it
-    constexpr int G = 128 / D;            // heads per CTA
-    constexpr int DK = D / 16, DT = D / 8;
-    const uint32_t ra = smem_u32(att_raw);
-    uint8_t* sm = att_raw + (((ra + 1023u) & ~1023u) - ra);
-    const int hg = blockIdx.x, img = blockIdx.y;
-    const int qtiles = (L + 15) / 16;
-    const int lk_pad = (L + KC - 1) / KC * KC;      // == box rows (single key chunk: L <= KC)
-    const uint32_t tile_bytes = static_cast<uint32_t>(lk_pad) * 128u;
-    uint64_t* bar = reinterpret_cast<uint64_t*>(sm + 6 * tile_bytes);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nwarps = blockDim.x >> 5;
-    if (threadIdx.x == 0) {
-        mbar_init(bar, 1);
-        fence_barrier_init();
-        mbar_arrive_expect_tx(bar, 6 * tile_bytes);
-#pragma unroll
-        for (int m = 0; m < 3; ++m)
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-                tma_load_2d(sm + (m * 2 + h) * tile_bytes, &tmQKV, bar, m * C + hg * 128 + h * 64, img * L);
-    }
-    __syncthreads();
-    mbar_wait(bar, 0);
-
-    const int g = lane >> 2, t = lane & 3;
-    for (int task = warp; task < G * qtiles; task += nwarps) {
-        const int head = task % G;
-        const int q0 = (task / G) * 16;
-        const int half = (head * D) / 64;                 // which 64-column box
-        const int cbase = ((head * D) % 64) / 8;          // first 16-byte chunk of this head in the 128-byte row
-        uint8_t* Qt = sm + (0 * 2 + half) * tile_bytes;
-        const uint8_t* Kt = sm + (1 * 2 + half) * tile_bytes;
-        const uint8_t* Vt = sm + (2 * 2 + half) * tile_bytes;
-        uint32_t qa[DK][4];
-#pragma unroll
-        for (int ks = 0; ks < DK; ++ks) {
-            const int qrow = q0 + (lane & 7) + (((lane >> 3) & 1) << 3);
-            ldmatrix_x4(qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], att_addr<true>(Qt, qrow, cbase + ks * 2 + (lane >> 4), 0));
-        }
-        float o[DT][4];
-        if (L > KC - 16) attend_qtile<D, KC, F16, true, 128, true>(qa, Kt, Vt, L, lk_pad, scale_log2e, lane, o, cbase);
-        else attend_qtile<D, KC, F16, true, 128, false>(qa, Kt, Vt, L, lk_pad, scale_log2e, lane, o, cbase);
-        // this task is the only reader of its 16 x D patch of the Q tile: reuse it as the output stage
-        __syncwarp();
-#pragma unroll
-        for (int dt = 0; dt < DT; ++dt) {
-            const int r0 = q0 + g, r1 = q0 + g + 8;
-            *reinterpret_cast<uint32_t*>(Qt + r0 * 128 + (((cbase + dt) ^ (r0 & 7)) << 4) + 4 * t) = pack2<F16>(o[dt][0], o[dt][1]);
-            *reinterpret_cast<uint32_t*>(Qt + r1 * 128 + (((cbase + dt) ^ (r1 & 7)) << 4) + 4 * t) = pack2<F16>(o[dt][2], o[dt][3]);
-        }
-    }
-    __syncthreads();
-    bf16* ob = out + static_cast<size_t>(img) * L * C + hg * 128;
-    for (int i = threadIdx.x; i < L * 16; i += blockDim.x) {
-        const int r = i >> 4, j = i & 15;
-        const uint8_t* src = sm + (j >> 3) * tile_bytes + r * 128 + (((j & 7) ^ (r & 7)) << 4);
-        *reinterpret_cast<uint4*>(ob + static_cast<size_t>(r) * C + j * 8) = *reinterpret_cast<const uint4*>(src);
-    }
 }
 
 // ---------------------------------------------------------------------------- persistent, double-buffered

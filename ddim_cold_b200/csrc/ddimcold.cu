@@ -16,7 +16,6 @@
 #include "elementwise.cuh"
 #include "gemm2.cuh"
 #include "block_tail.cuh"
-#include "attention_tc.cuh"
 #include "attention_fa.cuh"
 #include "fp32_path.cuh"
 
@@ -221,10 +220,8 @@ template <bool F16>
 static int launch_block_tail_inst(const CUtensorMap& tmO, const CUtensorMap& tmWp, const CUtensorMap& tmW1,
                                   const CUtensorMap& tmW2, const CUtensorMap& tmXld, const CUtensorMap& tmXst,
                                   const CUtensorMap& tmXN, BlockTailParams p, cudaStream_t st) {
-    // Sixteen epilogue warps (DDC_TAIL_GROUPS=4) measured SLOWER than eight (129 vs 117 us): the passes are paced by
-    // TMEM read bandwidth (64 B/clk/SM, five 196 KB passes per tile) and per-chunk hand-shakes, not by warp count.
-    if (env_int("DDC_TAIL_GROUPS", 2) == 4)
-        return launch_block_tail_ng<F16, 4>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, p, st);
+    // Two epilogue groups of four warps.  Sixteen epilogue warps measured SLOWER (129 vs 117 us): the passes are paced by
+    // TMEM reads and per-chunk hand-shakes, not by warp count, and 640 threads leave 96 registers each.
     return launch_block_tail_ng<F16, 2>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, p, st);
 }
 
@@ -290,36 +287,14 @@ static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads
     CK(cudaGetDevice(&dev));
     if (!(attr_dev_mask & (1 << dev))) {
         CK(cudaFuncSetAttribute(attention_head_kernel<D, KC, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        CK(cudaFuncSetAttribute(attention_group_kernel<D, KC, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         CK(cudaFuncSetAttribute(attention_stream_kernel<D, KC, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_dev_mask |= (1 << dev);
     }
     const float scale_log2e = (1.0f / sqrtf(static_cast<float>(D))) * 1.44269504088896340736f;
     const int qtiles = (L + 15) / 16;
-    constexpr int G = 128 / D;
     const int lk_pad = (L + KC - 1) / KC * KC;
-    const size_t gsmem = att_group_smem_bytes(L, KC);
     const size_t ssmem = att_stream_smem_bytes(L, KC);
-    if (D == 32 && attention_tc_usable(L, C, heads) && env_int("DDC_ATT_TC", 0)) {
-        // tcgen05 path: both contractions as UMMA, softmax from TMEM (attention_tc.cuh).  Opt-in: correct, but at
-        // L = 65 its per-item chain (TMA -> S MMA -> softmax -> P*V MMA -> output, ~5k cycles with two items in
-        // flight per SM) measures 70 - 160 us against 58 us for the warp-level kernel, which keeps 15 items in flight.
-        static int tc_attr_mask = 0;
-        if (!(tc_attr_mask & (1 << dev))) {
-            CK(cudaFuncSetAttribute(attention_tc_kernel<F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATC_SMEM_BYTES));
-            tc_attr_mask |= (1 << dev);
-        }
-        CUtensorMap tmq, tmkv;
-        TRY(make_tmap(&tmq, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, 64));
-        TRY(make_tmap(&tmkv, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, ATC_KEYS));
-        const int n_hg = C / 64;
-        const int n_items = B * n_hg;
-        const uint32_t magic = n_hg > 1 ? static_cast<uint32_t>((1ull << 32) / static_cast<uint32_t>(n_hg)) + 1u : 0u;
-        int grid = 2 * num_sms();
-        if (grid > n_items) grid = n_items;
-        CK(launch_chain(attention_tc_kernel<F16>, dim3(grid), dim3(ATC_THREADS), static_cast<size_t>(ATC_SMEM_BYTES), st, 1, tmq, tmkv,
-                        qkv, out, L, C, n_items, magic, scale_log2e));
-    } else if (C % 64 == 0 && L <= KC && lk_pad <= 256 && ssmem <= 75 * 1024 && !env_int("DDC_ATT_ONESHOT", 0)) {
+    if (C % 64 == 0 && L <= KC && lk_pad <= 256 && ssmem <= 75 * 1024) {
         // persistent CTAs, next item's tiles in flight while this one is computed
         CUtensorMap tm;
         TRY(make_tmap(&tm, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, lk_pad));
@@ -334,12 +309,6 @@ static int launch_att(const bf16* qkv, bf16* out, int B, int L, int C, int heads
         if (grid > n_items) grid = n_items;
         CK(launch_chain(attention_stream_kernel<D, KC, F16>, dim3(grid), dim3(warps * 32), ssmem, st, 1, tm, out, L, C, n_items,
                         n_hg_magic, scale_log2e));
-    } else if (heads % G == 0 && L <= KC && lk_pad <= 256 && gsmem <= 100 * 1024) {      // one image's head group per CTA
-        CUtensorMap tm;
-        TRY(make_tmap(&tm, false, qkv, static_cast<uint64_t>(B) * L, static_cast<uint64_t>(3) * C, lk_pad));
-        const int warps = qtiles < ATT_GROUP_WARPS ? qtiles : ATT_GROUP_WARPS;
-        CK(launch_chain(attention_group_kernel<D, KC, F16>, dim3(heads / G, B), dim3(warps * 32), gsmem, st, 1, tm, out, L, C,
-                        scale_log2e));
     } else {
         const size_t smem = att_head_smem_bytes(L, D, KC);
         if (smem > 227 * 1024) return fail(DDC_E_INVALID, "attention: L=%d needs %zu B of shared memory", L, smem);

@@ -218,17 +218,6 @@ def test_attention_legacy_long_sequence_kernel(lib, B, L, Cdim, heads, fmt, monk
     test_attention(lib, B, L, Cdim, heads, fmt)
 
 
-@pytest.mark.parametrize("B,L,Cdim,heads", [(3, 65, 384, 12), (300, 65, 384, 12), (3, 65, 128, 4), (7, 65, 64, 2), (1, 65, 192, 6)])
-@pytest.mark.parametrize("fmt", [0, 1])
-def test_attention_tcgen05_variant(lib, B, L, Cdim, heads, fmt, monkeypatch):
-    """The opt-in UMMA attention (attention_tc.cuh: head_dim 32, L = 65) against the same reference; the last token of
-    every image takes its CUDA-core side path, keys 65..79 of the 80-row boxes are masked."""
-    monkeypatch.setenv("DDC_ATT_TC", "1")
-    test_attention(lib, B, L, Cdim, heads, fmt)
-    monkeypatch.setenv("DDC_ATT_TC", "0")
-    test_attention(lib, B, L, Cdim, heads, fmt)
-
-
 @pytest.mark.parametrize("B,H,W,p", [(3, 64, 64, 8), (2, 64, 64, 4), (1, 200, 200, 8), (2, 16, 16, 4), (2, 32, 48, 4)])
 @pytest.mark.parametrize("fmt", [0, 1])
 def test_patchify(lib, B, H, W, p, fmt):
