@@ -1271,6 +1271,17 @@ extern "C" int ddc_k_affine(const float* in, float* out, size_t n, float add, fl
     return DDC_OK;
 }
 
+extern "C" int ddc_k_mix(const float* z, const float* draft, float* out, size_t n, size_t period, float a, float b, void* stream) {
+    if (z == nullptr || draft == nullptr || out == nullptr || period == 0) return fail(DDC_E_INVALID, "bad argument");
+    if (n == 0) return DDC_OK;
+    size_t blocks = (n + 255) / 256;
+    const size_t cap = static_cast<size_t>(num_sms()) * 16;
+    if (blocks > cap) blocks = cap;
+    mix_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(z, draft, out, n, period, a, b);
+    CK(cudaGetLastError());
+    return DDC_OK;
+}
+
 extern "C" int ddc_k_head_ddim(const float* y, int32_t ldy, float* x, int32_t batch, int32_t H, int32_t W, int32_t patch,
                                const ddc_step* host_step, float* x0_out, float* eps_out, void* stream) {
     if (y == nullptr || x == nullptr || host_step == nullptr || batch <= 0 || patch <= 0 || H % patch || W % patch)

@@ -336,6 +336,16 @@ __global__ void __launch_bounds__(256) affine_kernel(const float* __restrict__ i
         out[i] = (in[i] + add) * mul;
 }
 
+// out[i] = a * z[i] + b * draft[i % period]: the draft->drawing start state x = N(0,1) * sqrt(1 - alpha) + draft * sqrt(alpha)
+// (ViT_draft2drawing.py:396) for a batch of noise draws and one draft (period = 3*H*W) or one draft per image (period = n).
+// Separate roundings for the two products and the sum, like the reference's tensor expression (no FMA contraction).
+__global__ void __launch_bounds__(256) mix_kernel(const float* __restrict__ z, const float* __restrict__ draft, float* __restrict__ out,
+                                                  size_t n, size_t period, float a, float b) {
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n; i += stride)
+        out[i] = __fadd_rn(__fmul_rn(z[i], a), __fmul_rn(draft[i % period], b));
+}
+
 __global__ void copy_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, size_t n) {
     for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
          i += static_cast<size_t>(gridDim.x) * blockDim.x)

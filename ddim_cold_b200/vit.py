@@ -360,16 +360,29 @@ class DiffusionVisionTransformer(nn.Module):
         return [(x_init + 1) / 2] + [(seq[i] + 1) / 2 for i in range(n)]
 
     @torch.no_grad()
-    def draft2drawing(self, device, draft, t_start, k=10, N=1, noise=None):
+    def draft2drawing(self, device, draft, t_start, k=10, N=1, noise=None, return_on_device=False):
         """Batched form of the draft->drawing script loop (reference ViT_draft2drawing.py:391-409):
         x = N(0,1)*sqrt(1-a) + draft*sqrt(a), a = 1-sqrt(t_start/T); DDIM from t_start.
-        draft: [3,H,W] or [N,3,H,W] in [-1,1].  Returns CPU (x0+1)/2."""
+        draft: [3,H,W] or [N,3,H,W] in [-1,1]; noise: [N,3,H,W] on the CPU or already on `device` (then nothing but the
+        draft crosses PCIe, which is what a sweep over t_start wants).  Returns (x0+1)/2 on the CPU, or on `device`."""
         table, n = _lib.ddim_table(k, self.total_steps, t_start)
         alpha = 1 - math.sqrt(t_start / self.total_steps)
-        z = torch.normal(0, 1, (N, 3, self.img_size[0], self.img_size[1])) if noise is None \
-            else noise.detach().float().cpu()
-        x = z * math.sqrt(1 - alpha) + draft.detach().float().cpu() * math.sqrt(alpha)
-        img, _, _ = self._run_loop(device, x, table, n, affine=(1.0, 0.5))
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError(f"ddim_cold_b200 computes on CUDA (sm_100a) only; there is no CPU path. Got device={dev}.")
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        z = torch.normal(0, 1, (N, 3, self.img_size[0], self.img_size[1])) if noise is None else noise.detach().float()
+        if z.device.type != "cuda":
+            z = (z if z.is_pinned() else z.pin_memory()).to(dev, non_blocking=True)
+        z = z.contiguous()
+        d = draft.detach().float().to(dev).contiguous()
+        if d.numel() not in (z.numel(), z[0].numel()):
+            raise RuntimeError(f"draft of shape {tuple(draft.shape)} matches neither one image nor the batch {tuple(z.shape)}")
+        x = torch.empty_like(z)
+        _lib.check(_lib.load().ddc_k_mix(z.data_ptr(), d.data_ptr(), x.data_ptr(), z.numel(), d.numel(), math.sqrt(1 - alpha),
+                                         math.sqrt(alpha), torch.cuda.current_stream(dev).cuda_stream))
+        img, _, _ = self._run_loop(dev, x, table, n, keep_on_device=return_on_device, affine=(1.0, 0.5))
         return img
 
     @torch.no_grad()

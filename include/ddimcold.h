@@ -209,6 +209,12 @@ int ddc_k_head_ddim(const float* y, int32_t ldy, float* x, int32_t batch, int32_
  * value is (x0 + 1) / 2 (reference ViT.py:237, ViT_draft2drawing.py:288): applied on the device before the copy back. */
 int ddc_k_affine(const float* in, float* out, size_t n, float add, float mul, void* stream);
 
+/* out[i] = a * z[i] + b * draft[i % period] over n floats: the draft->drawing start state
+ * x = N(0,1) * sqrt(1 - alpha) + draft * sqrt(alpha) (reference ViT_draft2drawing.py:395-396), one draft for the whole
+ * batch (period = 3*H*W) or one per image (period = n); each product and the sum rounded separately like the reference's
+ * tensor expression.  in-place (out == z) allowed. */
+int ddc_k_mix(const float* z, const float* draft, float* out, size_t n, size_t period, float a, float b, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

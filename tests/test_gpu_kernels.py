@@ -258,3 +258,19 @@ def test_head_ddim(lib, B, H, W, p, t, k):
     assert np.array_equal(x0.cpu().numpy(), x0_ref)                      # pure data movement + clamp: bit exact
     assert np.abs(x.cpu().numpy() - xn_ref).max() < 1e-5 * max(1.0, np.abs(xn_ref).max())
     assert np.abs(eps.cpu().numpy() - eps_ref).max() < 1e-5 * max(1.0, np.abs(eps_ref).max())
+
+
+@pytest.mark.parametrize("N,per_image_draft", [(5, False), (3, True)])
+def test_mix_matches_reference_expression_bitwise(lib, N, per_image_draft):
+    """Draft->drawing start state (ViT_draft2drawing.py:395-396): noise * sqrt(1 - a) + draft * sqrt(a) with the reference's
+    three separate roundings -- bit-identical to the torch CPU expression."""
+    a = 1 - math.sqrt(1599 / 2000)
+    z = torch.randn(N, 3, 16, 24)
+    draft = torch.rand((N, 3, 16, 24) if per_image_draft else (3, 16, 24)) * 2 - 1
+    want = z * math.sqrt(1 - a) + draft * math.sqrt(a)
+    zc, dc = z.cuda(), draft.cuda()
+    out = torch.empty_like(zc)
+    _check(lib.ddc_k_mix(zc.data_ptr(), dc.data_ptr(), out.data_ptr(), zc.numel(), dc.numel(), math.sqrt(1 - a), math.sqrt(a),
+                         _stream()))
+    torch.cuda.synchronize()
+    assert torch.equal(out.cpu(), want)
