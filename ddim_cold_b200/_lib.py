@@ -57,6 +57,7 @@ SIGNATURES = {
     "ddc_k_embed": (C.c_int, [_i32] * 6 + [_vp] * 10),
     "ddc_k_block_tail": (C.c_int, [_i32, _i32, _i32] + [_vp] * 14),
     "ddc_k_attention": (C.c_int, [_i32, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
+    "ddc_k_qkv_attn": (C.c_int, [_i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "ddc_k_patchify": (C.c_int, [_i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
     "ddc_k_affine": (C.c_int, [_vp, _vp, _sz, C.c_float, C.c_float, _vp]),
     "ddc_k_mix": (C.c_int, [_vp, _vp, _vp, _sz, _sz, C.c_float, C.c_float, _vp]),

@@ -18,6 +18,7 @@
 #include "block_tail.cuh"
 #include "attention_fa.cuh"
 #include "fp32_path.cuh"
+#include "qkv_attn.cuh"
 
 using namespace ddc;
 
@@ -72,7 +73,8 @@ static int get_encode_fn(EncodeTiledFn* out) {
 }
 
 // [rows, cols] row-major tensor, 128-byte swizzle; the box is 128 bytes wide (64 bf16 or 32 fp32)
-static int make_tmap(CUtensorMap* m, bool f32, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+static int make_tmap(CUtensorMap* m, bool f32, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                     uint64_t row_stride_elems = 0) {
     EncodeTiledFn enc;
     TRY(get_encode_fn(&enc));
     const uint32_t box_cols = f32 ? 32 : 64;
@@ -81,7 +83,7 @@ static int make_tmap(CUtensorMap* m, bool f32, const void* base, uint64_t rows, 
         return fail(DDC_E_INVALID, "tensor map: rows=%llu cols=%llu box_rows=%u base=%p", (unsigned long long)rows,
                     (unsigned long long)cols, box_rows, base);
     cuuint64_t dims[2] = {cols, rows};
-    cuuint64_t strides[1] = {cols * esz};
+    cuuint64_t strides[1] = {(row_stride_elems ? row_stride_elems : cols) * esz};
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
@@ -338,12 +340,44 @@ static int run_attention(const bf16* qkv, bf16* out, int B, int L, int C, int he
     return fail(DDC_E_INVALID, "attention: head_dim %d unsupported (32 or 64)", D);
 }
 
+// ------------------------------------------------------------------------------- fused qkv + attention launch
+// DDC_QKV_ATTN=0 falls back to the separate qkv GEMM and attention kernels.
+static bool qkv_attn_usable(int L, int C, int heads) {
+    return L == QA_L && heads > 0 && C % heads == 0 && C / heads == 32 && C % 64 == 0 && C <= 384 && env_int("DDC_QKV_ATTN", 1) != 0;
+}
+
+template <bool F16>
+static int launch_qkv_attn(const CUtensorMap& tmA, const CUtensorMap& tmW, QkvAttnParams p, cudaStream_t st) {
+    static int attr_dev_mask = 0;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    auto kern = qkv_attn_kernel<F16>;
+    if (!(attr_dev_mask & (1 << dev))) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_dev_mask |= (1 << dev);
+    }
+    int stages = static_cast<int>((227 * 1024 - static_cast<long>(qkv_attn_smem_bytes(p.C, 0))) / (96 * 128));
+    if (stages > 8) stages = 8;
+    if (stages < 2) return fail(DDC_E_INVALID, "qkv+attention: C=%d leaves no room for the weight ring", p.C);
+    p.stages = stages;
+    p.n_hg = p.C / 64;
+    p.num_tp = (p.B + 3) / 4;
+    p.scale_log2e = (1.0f / sqrtf(32.0f)) * 1.44269504088896340736f;
+    int grid = 2 * p.num_tp < num_sms() ? 2 * p.num_tp : num_sms();
+    grid = grid / 2 * 2;
+    CK(launch_chain(kern, dim3(grid), dim3(QA_THREADS), qkv_attn_smem_bytes(p.C, stages), st, 2, tmA, tmW, p));
+    return DDC_OK;
+}
+
 // ------------------------------------------------------------------------------- plan
 struct LayerW {
     float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *b_qkv, *b_proj, *b_fc1, *b_fc2;
     bf16 *w_qkv, *w_proj, *w_fc1, *w_fc2;
     CUtensorMap tm_qkv[2], tm_proj[2], tm_fc1[2], tm_fc2[2];   // W tile boxes for cluster size 1 and 2
     CUtensorMap tm_fc1_tail;                                  // fc1 as 64-row half tiles (fused block tail)
+    bf16* w_qkv_hp;                                           // qkv weight rows regrouped per head pair (fused qkv + attention)
+    float* b_qkv_hp;
+    CUtensorMap tm_qkv_hp;                                    // box 64 x 96
 };
 
 struct GraphKey {
@@ -381,6 +415,9 @@ struct ddc_plan {
     float* Y;
     StepEntry* tbl;
     int* ctr;
+    bf16* QKVcls;                            // [maxB, 3C] q | k | v of the class rows (fused qkv + attention)
+    CUtensorMap tm_XN64, tm_XNcls, st_QKVcls; // XN as 64-row boxes; XN's class rows (row stride L*C); store map of QKVcls
+    bool no_fused_qkv;                       // set while a call runs on a work view that has no QKVcls buffer
     CUtensorMap tm_Ap, tm_O, tm_Hd, tm_XN;   // A-operand loads (box 64 x 128, padded row count)
     CUtensorMap tm_Xld;                      // residual loads (fp32, box 32 x 32, padded row count)
     // store maps are clipped to exactly batch*L rows, so they are rebuilt when the batch changes
@@ -447,6 +484,7 @@ static void carve(ddc_plan* pl, void* weight_arena, void* work_arena, size_t* wb
         l.ln2_g = w.take<float>(C);  l.ln2_b = w.take<float>(C);
         l.w_fc1 = w.take<bf16>(C * C);  l.b_fc1 = w.take<float>(C);
         l.w_fc2 = w.take<bf16>(C * C);  l.b_fc2 = w.take<float>(C);
+        l.w_qkv_hp = w.take<bf16>(3 * C * C);  l.b_qkv_hp = w.take<float>(3 * C);
     }
     pl->lnf_g = w.take<float>(C);
     pl->lnf_b = w.take<float>(C);
@@ -464,6 +502,7 @@ static void carve(ddc_plan* pl, void* weight_arena, void* work_arena, size_t* wb
     pl->Y = k.take<float>(Mp * P);
     pl->tbl = k.take<StepEntry>(s.total_steps);
     pl->ctr = k.take<int>(64);
+    pl->QKVcls = k.take<bf16>(static_cast<size_t>(pl->maxB) * 3 * C);
     *kbytes = (k.off + 255) & ~static_cast<size_t>(255);
 }
 
@@ -534,6 +573,10 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
     mk(&pl->tm_XN, false, pl->XN, Mp, C, G2_BM);
     mk(&pl->tm_Xld, true, pl->X, Mp, C, G2_BM);
     mk(&pl->tm_posb, true, pl->posb, static_cast<uint64_t>(pl->L) + 127, C, G2_BM);
+    mk(&pl->tm_XN64, false, pl->XN, Mp, C, 64);
+    if (r == DDC_OK) r = make_tmap(&pl->tm_XNcls, false, pl->XN, static_cast<uint64_t>(pl->maxB), C, G2_BM, static_cast<uint64_t>(pl->L) * C);
+    for (auto& l : pl->layers) mk(&l.tm_qkv_hp, false, l.w_qkv_hp, 3 * C, C, 96);
+    pl->no_fused_qkv = false;
     for (int cs = 1; cs <= 2; ++cs) {
         mk(&pl->tm_wpatch[cs - 1], false, pl->w_patch, C, pl->Kp, pl->bn_row / cs);
         mk(&pl->tm_whead[cs - 1], false, pl->w_head, pl->P, C, pl->bn_head / cs);
@@ -631,6 +674,7 @@ extern "C" int ddc_pack_weights(ddc_plan* pl, const float* const* t, int32_t n_t
         LayerW& l = pl->layers[i];
         copy(b[0], l.ln1_g, C);  copy(b[1], l.ln1_b, C);
         pack(b[2], l.w_qkv, 3 * C, C, C);  copy(b[3], l.b_qkv, 3 * C);
+        if (!pl->f32) repack_qkv_hp_kernel<<<296, 64, 0, st>>>(l.w_qkv, l.b_qkv, l.w_qkv_hp, l.b_qkv_hp, C);
         pack(b[4], l.w_proj, C, C, C);  copy(b[5], l.b_proj, C);
         copy(b[6], l.ln2_g, C);  copy(b[7], l.ln2_b, C);
         pack(b[8], l.w_fc1, C, C, C);  copy(b[9], l.b_fc1, C);
@@ -692,6 +736,7 @@ static int ensure_store_maps(ddc_plan* pl, int B) {
     TRY(make_tmap(&pl->st_XN, false, pl->XN, M, C, G2_BM));
     TRY(make_tmap(&pl->st_X, true, pl->X, M, C, G2_BM));
     if (pl->P % 32 == 0) TRY(make_tmap(&pl->st_Y, true, pl->Y, M, pl->P, G2_BM));
+    if (!pl->no_fused_qkv) TRY(make_tmap(&pl->st_QKVcls, false, pl->QKVcls, static_cast<uint64_t>(B), 3 * C, G2_BM));
     pl->maps_B = B;
     if (pl->gexec) {                 // the captured graph holds the old maps by value
         cudaGraphExecDestroy(pl->gexec);
@@ -810,12 +855,26 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
     for (int i = 0; i < s.depth; ++i) {
         LayerW& l = pl->layers[i];
         Gemm2Params q{};
-        q.M = M; q.N = 3 * C; q.K = C; q.bn = pl->bn_qkv; q.stages = pick_stages2(q.K, q.N, q.bn / cs, false);
-        q.bias = l.b_qkv;
-        TRY((launch_gemm2<S_BF16>(pl->tm_XN, l.tm_qkv[cs - 1], pl->st_QKV, pl->tm_Xld, pl->st_XN, q, f16, cs, st)));
-        MARK(KC_QKV);
-        TRY(run_attention(pl->QKV, pl->O, B, L, C, s.heads, f16, st));
-        MARK(KC_ATTN);
+        q.N = 3 * C; q.K = C; q.bn = pl->bn_qkv; q.bias = l.b_qkv;
+        if (!pl->no_fused_qkv && qkv_attn_usable(L, C, s.heads)) {
+            // q | k | v of the class rows (one per image: a [B x 3C] GEMM over XN rows L apart), then qkv + attention of
+            // the patch rows in one kernel that reads those class rows from L2
+            const int ccs = gemm_cluster_size(B);
+            q.M = B; q.stages = pick_stages2(q.K, q.N, q.bn / ccs, false);
+            TRY((launch_gemm2<S_BF16>(pl->tm_XNcls, l.tm_qkv[ccs - 1], pl->st_QKVcls, pl->tm_Xld, pl->st_XN, q, f16, ccs, st)));
+            MARK(KC_QKV);
+            QkvAttnParams qa{};
+            qa.B = B; qa.C = C; qa.bias_hp = l.b_qkv_hp; qa.qkv_cls = pl->QKVcls; qa.out = pl->O;
+            if (f16) TRY(launch_qkv_attn<true>(pl->tm_XN64, l.tm_qkv_hp, qa, st));
+            else TRY(launch_qkv_attn<false>(pl->tm_XN64, l.tm_qkv_hp, qa, st));
+            MARK(KC_ATTN);
+        } else {
+            q.M = M; q.stages = pick_stages2(q.K, q.N, q.bn / cs, false);
+            TRY((launch_gemm2<S_BF16>(pl->tm_XN, l.tm_qkv[cs - 1], pl->st_QKV, pl->tm_Xld, pl->st_XN, q, f16, cs, st)));
+            MARK(KC_QKV);
+            TRY(run_attention(pl->QKV, pl->O, B, L, C, s.heads, f16, st));
+            MARK(KC_ATTN);
+        }
         const float* lnn_g = (i + 1 < s.depth) ? pl->layers[i + 1].ln1_g : pl->lnf_g;
         const float* lnn_b = (i + 1 < s.depth) ? pl->layers[i + 1].ln1_b : pl->lnf_b;
         if (block_tail_usable(M, C, pl->bn_row)) {
@@ -977,7 +1036,9 @@ extern "C" int ddc_forward_fixed_scratch(ddc_plan* pl, const float* x, const int
     ddc_plan::WorkView own;
     view_save(pl, &own);
     view_install(pl, &pl->fixed_view);
+    pl->no_fused_qkv = true;              // the built-in array is laid out for the separate qkv GEMM and attention kernels
     int rc = enqueue_predictor(pl, x, batch, t, false, st);
+    pl->no_fused_qkv = false;
     if (rc == DDC_OK) {
         HeadDdimParams q{};
         q.y = pl->Y; q.ldy = pl->P; q.x = out;
@@ -1244,6 +1305,32 @@ extern "C" int ddc_k_attention(int32_t fmt, const void* qkv, void* out, int32_t 
     if (qkv == nullptr || out == nullptr || batch <= 0 || L <= 0) return fail(DDC_E_INVALID, "bad argument");
     return run_attention(static_cast<const bf16*>(qkv), static_cast<bf16*>(out), batch, L, C, heads, fmt == 1,
                          static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int ddc_k_qkv_attn(int32_t fmt, const void* xn, const void* w_qkv, const float* b_qkv, void* out, int32_t batch, int32_t C,
+                              int32_t heads, void* w_hp, float* b_hp, void* qkv_cls, void* stream) {
+    if (!xn || !w_qkv || !b_qkv || !out || !w_hp || !b_hp || !qkv_cls || batch <= 0) return fail(DDC_E_INVALID, "bad argument");
+    if (!qkv_attn_usable(QA_L, C, heads)) return fail(DDC_E_INVALID, "qkv+attention: needs 65 tokens, head_dim 32, embed_dim %% 64 == 0 and <= 384 (C=%d heads=%d)", C, heads);
+    const bool f16 = fmt == 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int L = QA_L, M = batch * L;
+    const uint64_t Mp = (static_cast<uint64_t>(M) + G2_BM - 1) / G2_BM * G2_BM;
+    repack_qkv_hp_kernel<<<296, 64, 0, st>>>(static_cast<const bf16*>(w_qkv), b_qkv, static_cast<bf16*>(w_hp), b_hp, C);
+    CK(cudaGetLastError());
+    CUtensorMap tmCls, tmW, tmO, tmA64, tmWhp;
+    const int cs = gemm_cluster_size(batch);
+    const int bn = pick_bn_stream(3 * C);
+    TRY(make_tmap(&tmCls, false, xn, static_cast<uint64_t>(batch), C, G2_BM, static_cast<uint64_t>(L) * C));
+    TRY(make_tmap(&tmW, false, w_qkv, 3 * static_cast<uint64_t>(C), C, bn / cs));
+    TRY(make_tmap(&tmO, false, qkv_cls, static_cast<uint64_t>(batch), 3 * static_cast<uint64_t>(C), G2_BM));
+    Gemm2Params q{};
+    q.M = batch; q.N = 3 * C; q.K = C; q.bn = bn; q.stages = pick_stages2(C, 3 * C, bn / cs, false); q.bias = b_qkv;
+    TRY((launch_gemm2<S_BF16>(tmCls, tmW, tmO, tmCls, tmCls, q, f16, cs, st)));
+    TRY(make_tmap(&tmA64, false, xn, Mp, C, 64));
+    TRY(make_tmap(&tmWhp, false, w_hp, 3 * static_cast<uint64_t>(C), C, 96));
+    QkvAttnParams qa{};
+    qa.B = batch; qa.C = C; qa.bias_hp = b_hp; qa.qkv_cls = static_cast<const bf16*>(qkv_cls); qa.out = static_cast<bf16*>(out);
+    return f16 ? launch_qkv_attn<true>(tmA64, tmWhp, qa, st) : launch_qkv_attn<false>(tmA64, tmWhp, qa, st);
 }
 
 extern "C" int ddc_k_patchify(int32_t fmt, const float* x, void* ap, int32_t batch, int32_t H, int32_t W, int32_t patch, int32_t Kp,

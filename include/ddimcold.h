@@ -195,6 +195,15 @@ int ddc_k_block_tail(int32_t fmt, int32_t M, int32_t C, const void* O, const voi
  * qkv: bf16 [B*L, 3C] (column s*C + head*d + e); out: bf16 [B*L, C]. */
 int ddc_k_attention(int32_t fmt, const void* qkv, void* out, int32_t batch, int32_t L, int32_t C, int32_t heads, void* stream);
 
+/* qkv Linear and attention of a block in one kernel, for 65-token images with heads of 32 (reference ViT.py:105-114 up to
+ * the projection): out[b*65 + l, :] = concat_h softmax(q_h k_h^T / sqrt(32)) v_h with q | k | v = xn * w_qkv^T + b_qkv, the
+ * q / k / v values never written to global memory (except the class rows).  xn: 16-bit [m_pad, C] (LayerNorm output, rows
+ * allocated to a multiple of 128); w_qkv: 16-bit [3C, C]; b_qkv: fp32 [3C]; out: 16-bit [batch*65, C].  Caller-provided
+ * scratch: w_hp 16-bit [3C, C] and b_hp fp32 [3C] (the weight regrouped per head pair), qkv_cls 16-bit [batch, 3C].
+ * C % 64 == 0, C <= 384, C / heads == 32. */
+int ddc_k_qkv_attn(int32_t fmt, const void* xn, const void* w_qkv, const float* b_qkv, void* out, int32_t batch, int32_t C,
+                   int32_t heads, void* w_hp, float* b_hp, void* qkv_cls, void* stream);
+
 /* Patchify (im2col of the stride-p conv, reference ViT.py:150,154): x fp32 [B,3,H,W] ->
  * ap bf16 [B*L, Kp] with a zero cls row per image and zero K padding. */
 int ddc_k_patchify(int32_t fmt, const float* x, void* ap, int32_t batch, int32_t H, int32_t W, int32_t patch, int32_t Kp,

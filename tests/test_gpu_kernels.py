@@ -274,3 +274,33 @@ def test_mix_matches_reference_expression_bitwise(lib, N, per_image_draft):
                          _stream()))
     torch.cuda.synchronize()
     assert torch.equal(out.cpu(), want)
+
+
+@pytest.mark.parametrize("B,Cdim,heads", [(4, 384, 12), (5, 128, 4), (1, 64, 2), (301, 384, 12), (130, 256, 8), (2, 192, 6)])
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_qkv_attention_fused(lib, B, Cdim, heads, fmt):
+    """qkv Linear + attention in one kernel (qkv_attn.cuh) for 65-token images: against fp32 torch, with q/k/v rounded to
+    the operand format as the kernel does.  Batches that are not a multiple of four leave part of the last CTA pair empty;
+    class-token rows take their q/k/v from the separate class-row GEMM."""
+    L, d = 65, 32
+    g = torch.Generator(device="cuda").manual_seed(B * 7 + Cdim)
+    M = B * L
+    xn = _pad_rows(_op(torch.randn(M, Cdim, device="cuda", generator=g), fmt))
+    W = _op(torch.randn(3 * Cdim, Cdim, device="cuda", generator=g) * (1.5 / math.sqrt(Cdim)), fmt)
+    b = torch.randn(3 * Cdim, device="cuda", generator=g) * 0.2
+    out = torch.full((M + 3, Cdim), 7.0, device="cuda", dtype=W.dtype)
+    before = out.clone()
+    w_hp = torch.empty_like(W)
+    b_hp = torch.empty_like(b)
+    qkv_cls = torch.empty(B, 3 * Cdim, device="cuda", dtype=W.dtype)
+    _check(lib.ddc_k_qkv_attn(fmt, xn.data_ptr(), W.data_ptr(), b.data_ptr(), out.data_ptr(), B, Cdim, heads, w_hp.data_ptr(),
+                              b_hp.data_ptr(), qkv_cls.data_ptr(), _stream()))
+    torch.cuda.synchronize()
+    qkv = _op(xn[:M].float() @ W.float().T + b, fmt).float()
+    x = qkv.reshape(B, L, 3, heads, d).permute(2, 0, 3, 1, 4)
+    q, k, v = x[0], x[1], x[2]
+    pr = ((q @ k.transpose(-2, -1)) * d ** -0.5).softmax(dim=-1)
+    ref = (pr @ v).transpose(1, 2).reshape(M, Cdim)
+    err = (out[:M].float() - ref).abs().max().item()
+    assert err < 2e-2 * max(1.0, ref.abs().max().item()), err
+    assert torch.equal(out[M:], before[M:]), "rows beyond M were written"
