@@ -417,7 +417,6 @@ struct ddc_plan {
     int* ctr;
     bf16* QKVcls;                            // [maxB, 3C] q | k | v of the class rows (fused qkv + attention)
     CUtensorMap tm_XN64, tm_XNcls, st_QKVcls; // XN as 64-row boxes; XN's class rows (row stride L*C); store map of QKVcls
-    bool no_fused_qkv;                       // set while a call runs on a work view that has no QKVcls buffer
     CUtensorMap tm_Ap, tm_O, tm_Hd, tm_XN;   // A-operand loads (box 64 x 128, padded row count)
     CUtensorMap tm_Xld;                      // residual loads (fp32, box 32 x 32, padded row count)
     // store maps are clipped to exactly batch*L rows, so they are rebuilt when the batch changes
@@ -434,7 +433,9 @@ struct ddc_plan {
         float* Y;
         StepEntry* tbl;
         int* ctr;
+        bf16* QKVcls;
         CUtensorMap tm_Ap, tm_O, tm_Hd, tm_XN, tm_Xld, st_QKV, st_Hd, st_XN, st_X, st_Y;
+        CUtensorMap tm_XN64, tm_XNcls, st_QKVcls;
         int maps_B, Mpad, maxB;
         cudaGraphExec_t gexec;
     };
@@ -576,7 +577,6 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
     mk(&pl->tm_XN64, false, pl->XN, Mp, C, 64);
     if (r == DDC_OK) r = make_tmap(&pl->tm_XNcls, false, pl->XN, static_cast<uint64_t>(pl->maxB), C, G2_BM, static_cast<uint64_t>(pl->L) * C);
     for (auto& l : pl->layers) mk(&l.tm_qkv_hp, false, l.w_qkv_hp, 3 * C, C, 96);
-    pl->no_fused_qkv = false;
     for (int cs = 1; cs <= 2; ++cs) {
         mk(&pl->tm_wpatch[cs - 1], false, pl->w_patch, C, pl->Kp, pl->bn_row / cs);
         mk(&pl->tm_whead[cs - 1], false, pl->w_head, pl->P, C, pl->bn_head / cs);
@@ -736,7 +736,7 @@ static int ensure_store_maps(ddc_plan* pl, int B) {
     TRY(make_tmap(&pl->st_XN, false, pl->XN, M, C, G2_BM));
     TRY(make_tmap(&pl->st_X, true, pl->X, M, C, G2_BM));
     if (pl->P % 32 == 0) TRY(make_tmap(&pl->st_Y, true, pl->Y, M, pl->P, G2_BM));
-    if (!pl->no_fused_qkv) TRY(make_tmap(&pl->st_QKVcls, false, pl->QKVcls, static_cast<uint64_t>(B), 3 * C, G2_BM));
+    TRY(make_tmap(&pl->st_QKVcls, false, pl->QKVcls, static_cast<uint64_t>(B), 3 * C, G2_BM));
     pl->maps_B = B;
     if (pl->gexec) {                 // the captured graph holds the old maps by value
         cudaGraphExecDestroy(pl->gexec);
@@ -856,7 +856,7 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
         LayerW& l = pl->layers[i];
         Gemm2Params q{};
         q.N = 3 * C; q.K = C; q.bn = pl->bn_qkv; q.bias = l.b_qkv;
-        if (!pl->no_fused_qkv && qkv_attn_usable(L, C, s.heads)) {
+        if (qkv_attn_usable(L, C, s.heads)) {
             // q | k | v of the class rows (one per image: a [B x 3C] GEMM over XN rows L apart), then qkv + attention of
             // the patch rows in one kernel that reads those class rows from L2
             const int ccs = gemm_cluster_size(B);
@@ -958,8 +958,9 @@ static size_t fixed_scratch_layout(const ddc_plan* pl, int B, ddc_plan::WorkView
     bf16* Ap = k.take<bf16>(Mp * Kp);
     bf16* XN = k.take<bf16>(Mp * C);
     float* Y = k.take<float>(Mp * P);
+    bf16* QKVcls = k.take<bf16>(static_cast<size_t>(B) * 3 * C);
     if (v != nullptr) {
-        v->X = X; v->QKV = QKV; v->O = O; v->Hd = Hd; v->Ap = Ap; v->XN = XN; v->Y = Y;
+        v->X = X; v->QKV = QKV; v->O = O; v->Hd = Hd; v->Ap = Ap; v->XN = XN; v->Y = Y; v->QKVcls = QKVcls;
         v->tbl = nullptr; v->ctr = nullptr;
         v->Mpad = static_cast<int>(Mp);
         v->maxB = B;
@@ -971,7 +972,8 @@ static size_t fixed_scratch_layout(const ddc_plan* pl, int B, ddc_plan::WorkView
 
 static void view_save(const ddc_plan* pl, ddc_plan::WorkView* v) {
     v->X = pl->X; v->QKV = pl->QKV; v->O = pl->O; v->Hd = pl->Hd; v->Ap = pl->Ap; v->XN = pl->XN; v->Y = pl->Y;
-    v->tbl = pl->tbl; v->ctr = pl->ctr;
+    v->tbl = pl->tbl; v->ctr = pl->ctr; v->QKVcls = pl->QKVcls;
+    v->tm_XN64 = pl->tm_XN64; v->tm_XNcls = pl->tm_XNcls; v->st_QKVcls = pl->st_QKVcls;
     v->tm_Ap = pl->tm_Ap; v->tm_O = pl->tm_O; v->tm_Hd = pl->tm_Hd; v->tm_XN = pl->tm_XN; v->tm_Xld = pl->tm_Xld;
     v->st_QKV = pl->st_QKV; v->st_Hd = pl->st_Hd; v->st_XN = pl->st_XN; v->st_X = pl->st_X; v->st_Y = pl->st_Y;
     v->maps_B = pl->maps_B; v->Mpad = pl->Mpad; v->maxB = pl->maxB; v->gexec = pl->gexec;
@@ -979,7 +981,8 @@ static void view_save(const ddc_plan* pl, ddc_plan::WorkView* v) {
 
 static void view_install(ddc_plan* pl, const ddc_plan::WorkView* v) {
     pl->X = v->X; pl->QKV = v->QKV; pl->O = v->O; pl->Hd = v->Hd; pl->Ap = v->Ap; pl->XN = v->XN; pl->Y = v->Y;
-    pl->tbl = v->tbl; pl->ctr = v->ctr;
+    pl->tbl = v->tbl; pl->ctr = v->ctr; pl->QKVcls = v->QKVcls;
+    pl->tm_XN64 = v->tm_XN64; pl->tm_XNcls = v->tm_XNcls; pl->st_QKVcls = v->st_QKVcls;
     pl->tm_Ap = v->tm_Ap; pl->tm_O = v->tm_O; pl->tm_Hd = v->tm_Hd; pl->tm_XN = v->tm_XN; pl->tm_Xld = v->tm_Xld;
     pl->st_QKV = v->st_QKV; pl->st_Hd = v->st_Hd; pl->st_XN = v->st_XN; pl->st_X = v->st_X; pl->st_Y = v->st_Y;
     pl->maps_B = v->maps_B; pl->Mpad = v->Mpad; pl->maxB = v->maxB; pl->gexec = v->gexec;
@@ -1027,6 +1030,8 @@ extern "C" int ddc_forward_fixed_scratch(ddc_plan* pl, const float* x, const int
         TRY(make_tmap(&v.tm_Hd, false, v.Hd, Mp, C, G2_BM));
         TRY(make_tmap(&v.tm_XN, false, v.XN, Mp, C, G2_BM));
         TRY(make_tmap(&v.tm_Xld, true, v.X, Mp, C, G2_BM));
+        TRY(make_tmap(&v.tm_XN64, false, v.XN, Mp, C, 64));
+        TRY(make_tmap(&v.tm_XNcls, false, v.XN, static_cast<uint64_t>(fit), C, G2_BM, static_cast<uint64_t>(pl->L) * C));
         pl->fixed_view = v;
         pl->fixed_view_cap = fit;
     }
@@ -1036,9 +1041,7 @@ extern "C" int ddc_forward_fixed_scratch(ddc_plan* pl, const float* x, const int
     ddc_plan::WorkView own;
     view_save(pl, &own);
     view_install(pl, &pl->fixed_view);
-    pl->no_fused_qkv = true;              // the built-in array is laid out for the separate qkv GEMM and attention kernels
     int rc = enqueue_predictor(pl, x, batch, t, false, st);
-    pl->no_fused_qkv = false;
     if (rc == DDC_OK) {
         HeadDdimParams q{};
         q.y = pl->Y; q.ldy = pl->P; q.x = out;
