@@ -346,6 +346,8 @@ static bool qkv_attn_usable(int L, int C, int heads) {
     return L == QA_L && heads > 0 && C % heads == 0 && C / heads == 32 && C % 64 == 0 && C <= 384 && env_int("DDC_QKV_ATTN", 1) != 0;
 }
 
+static long long* g_qa_trace = nullptr;      // tuning aid: ddc_dbg_qkv_attn_trace
+
 template <bool F16>
 static int launch_qkv_attn(const CUtensorMap& tmA, const CUtensorMap& tmW, QkvAttnParams p, cudaStream_t st) {
     static int attr_dev_mask = 0;
@@ -363,6 +365,7 @@ static int launch_qkv_attn(const CUtensorMap& tmA, const CUtensorMap& tmW, QkvAt
     p.n_hg = p.C / 64;
     p.num_tp = (p.B + 3) / 4;
     p.scale_log2e = (1.0f / sqrtf(32.0f)) * 1.44269504088896340736f;
+    p.trace = g_qa_trace;
     int grid = 2 * p.num_tp < num_sms() ? 2 * p.num_tp : num_sms();
     grid = grid / 2 * 2;
     CK(launch_chain(kern, dim3(grid), dim3(QA_THREADS), qkv_attn_smem_bytes(p.C, stages), st, 2, tmA, tmW, p));
@@ -1334,6 +1337,11 @@ extern "C" int ddc_k_qkv_attn(int32_t fmt, const void* xn, const void* w_qkv, co
     QkvAttnParams qa{};
     qa.B = batch; qa.C = C; qa.bias_hp = b_hp; qa.qkv_cls = static_cast<const bf16*>(qkv_cls); qa.out = static_cast<bf16*>(out);
     return f16 ? launch_qkv_attn<true>(tmA64, tmWhp, qa, st) : launch_qkv_attn<false>(tmA64, tmWhp, qa, st);
+}
+
+extern "C" int ddc_dbg_qkv_attn_trace(void* dev_buffer) {
+    g_qa_trace = static_cast<long long*>(dev_buffer);
+    return DDC_OK;
 }
 
 extern "C" int ddc_k_patchify(int32_t fmt, const float* x, void* ap, int32_t batch, int32_t H, int32_t W, int32_t patch, int32_t Kp,

@@ -8,8 +8,10 @@
 //                                                        are one 192-row tile; each CTA stages 96 of them)
 //     epilogue      TMEM -> + bias -> 16 bit -> the head pair's Q / K / V tiles of the CTA's two images in shared memory
 //                   (the class token's q / k / v row comes from a small GEMM over the class rows that ran just before)
-//     attention     one warp per (image, 16 query rows): both heads, mma.sync flash-style softmax(q k^T) v from shared
-//                   memory (attend_qtile of attention.cuh), output staged over the Q rows and written as 128-byte segments
+//     attention     one warp per (image, 16 patch query rows, head): mma.sync flash-style softmax(q k^T) v from shared
+//                   memory (attend_qtile of attention.cuh), output staged over the warp's own Q columns and written as
+//                   64-byte row segments; the class token's query row (one per image and head: 65 dot products and a
+//                   65-term sum) is done on the CUDA cores by the epilogue warps while the attention warps work
 //   the accumulator is double-buffered in TMEM, so the tensor core computes head pair hg + 1 while the warps work on hg.
 //
 // Why the class token is separate: 65 rows per image do not tile a 128-row MMA; 64 do.  Its q / k / v (one row per image)
@@ -21,7 +23,7 @@
 
 namespace ddc {
 
-constexpr int QA_THREADS = 640;       // warps 0,3 TMA, 1 MMA, 2 TMEM | 4-7 epilogue | 8-17 attention, 18-19 class rows
+constexpr int QA_THREADS = 768;       // warps 0,3 TMA, 1 MMA, 2 TMEM | 4-7 epilogue + class rows | 8-23 attention
 constexpr int QA_NB = 192;            // q | k | v rows of one head pair
 constexpr int QA_REG = 80 * 128;      // one image's Q (or K, or V) tile: 80 rows x 128 B (64 patches, class row, padding)
 constexpr int QA_L = 65;
@@ -32,7 +34,12 @@ struct QkvAttnParams {
     const bf16* qkv_cls;              // [B, 3C] q | k | v of the class rows (standard column order)
     bf16* out;                        // [B * 65, C]
     float scale_log2e;
+    long long* trace;                 // optional [4 roles][32 head-pair iterations][8 events] clock stamps of CTA 0 (tuning aid)
 };
+
+__device__ __forceinline__ void qa_stamp(const QkvAttnParams& p, int role, uint32_t it, int ev) {
+    if (p.trace != nullptr && blockIdx.x == 0 && it < 32u && (threadIdx.x & 31) == 0) p.trace[(role * 32 + it) * 8 + ev] = clock64();
+}
 
 inline size_t qkv_attn_smem_bytes(int C, int stages) {
     return 1024 + static_cast<size_t>(C / 64) * G2_A_KB_BYTES + static_cast<size_t>(stages) * 96 * 128 + 3 * 2 * QA_REG +
@@ -63,8 +70,8 @@ qkv_attn_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C] 16
     uint64_t* aempty_bar = bars + 24;     // [8] A K block no longer needed by this tile (pair commit)
     uint64_t* tfull_bar = bars + 32;      // [2] accumulator stage complete (pair commit)
     uint64_t* tempty_bar = bars + 34;     // [2] accumulator stage drained (leader: 4 epilogue warps x 2 CTAs)
-    uint64_t* ready_bar = bars + 36;      // [1] Q/K/V tiles of a head pair are in shared memory (4 epilogue + 2 class-row warps)
-    uint64_t* free_bar = bars + 37;       // [1] attention is done with them (10 warps)
+    uint64_t* ready_bar = bars + 36;      // [1] Q/K/V tiles of a head pair are in shared memory (4 epilogue warps)
+    uint64_t* free_bar = bars + 37;       // [1] everyone is done with them (16 attention warps + 4 class-query warps)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 40);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -85,8 +92,8 @@ qkv_attn_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C] 16
             mbar_init(&tfull_bar[i], 1);
             mbar_init(&tempty_bar[i], 8);
         }
-        mbar_init(ready_bar, 6);
-        mbar_init(free_bar, 10);
+        mbar_init(ready_bar, 4);
+        mbar_init(free_bar, 20);
         fence_barrier_init();
     }
     if (warp == 2) {
@@ -153,10 +160,12 @@ qkv_attn_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C] 16
                 const uint32_t acc = acc_it & 1u;
                 mbar_wait(&tempty_bar[acc], ((acc_it >> 1) & 1u) ^ 1u);
                 tc_fence_after();
+                qa_stamp(p, 0, acc_it, 0);
                 for (int kb = 0; kb < kblocks; ++kb) {
                     if (hg == 0) mbar_wait(&afull_bar[kb], tc & 1);
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
+                    if (kb == 0) qa_stamp(p, 0, acc_it, 1);
                     if (elect_one()) {
                         umma_kblock<2>(tb + acc * 256u, ad0 + static_cast<uint64_t>(kb * (G2_A_KB_BYTES >> 4)),
                                        bd0 + static_cast<uint64_t>(stage * (kWStage >> 4)), idesc, kb != 0 ? 1u : 0u);
@@ -167,6 +176,7 @@ qkv_attn_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C] 16
                     __syncwarp();
                     if (++stage == static_cast<uint32_t>(p.stages)) { stage = 0; phase ^= 1; }
                 }
+                qa_stamp(p, 0, acc_it, 2);
             }
         }
     } else if (warp >= 4 && warp < 8) {
@@ -176,13 +186,18 @@ qkv_attn_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C] 16
         const int reg = trow >> 6, lrow = trow & 63;
         const uint32_t lane_taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
         uint8_t* dst[3] = {smem_q + reg * QA_REG + lrow * 128, smem_k + reg * QA_REG + lrow * 128, smem_v + reg * QA_REG + lrow * 128};
+        const int cj = q >> 1, chd = q & 1;               // this warp's class query: image cj of the CTA, head chd of the pair
+        const int vch = chd * 4 + (lane >> 3), voff = (lane & 7) * 2;
         uint32_t acc_it = 0, hg_it = 0;
         for (int tp = first_tp; tp < p.num_tp; tp += tp_step) {
+            const int cimg = image_of(tp, cj);
             for (int hg = 0; hg < p.n_hg; ++hg, ++acc_it, ++hg_it) {
                 const uint32_t acc = acc_it & 1u;
                 mbar_wait(&tfull_bar[acc], (acc_it >> 1) & 1u);
                 tc_fence_after();
-                if (hg_it > 0) mbar_wait(free_bar, (hg_it - 1) & 1u);       // attention has left the previous head pair's tiles
+                if (q == 0) qa_stamp(p, 1, hg_it, 0);
+                if (hg_it > 0) mbar_wait(free_bar, (hg_it - 1) & 1u);       // everyone has left the previous head pair's tiles
+                if (q == 0) qa_stamp(p, 1, hg_it, 1);
                 const float* bias = smem_bias + hg * QA_NB;
 #pragma unroll
                 for (int c = 0; c < 6; ++c) {                               // 32 columns at a time: q 0-1, k 2-3, v 4-5
@@ -201,76 +216,129 @@ qkv_attn_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C] 16
                         *reinterpret_cast<uint4*>(row + ((((c & 1) * 4 + j) ^ (lrow & 7)) << 4)) = u;
                     }
                 }
+                // class token's k | v of image q (warps 0, 1) from the class-row GEMM -> key row 64 of that image's tiles
+                if (q < 2 && lane < 16 && image_of(tp, q) < p.B) {
+                    const int sk = lane >> 3, ch = lane & 7;
+                    const uint4 val = __ldg(reinterpret_cast<const uint4*>(p.qkv_cls + static_cast<size_t>(image_of(tp, q)) * 3 * p.C +
+                                                                           (1 + sk) * p.C + hg * 64) + ch);
+                    *reinterpret_cast<uint4*>((sk == 0 ? smem_k : smem_v) + q * QA_REG + 64 * 128 + (ch << 4)) = val;   // (64 & 7) = 0
+                }
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) {
                     mbar_arrive_leader(&tempty_bar[acc]);                   // the accumulator stage may be overwritten
                     mbar_arrive(ready_bar);
                 }
+                if (q == 0) qa_stamp(p, 1, hg_it, 2);
+                // ---- class token's query row of (cimg, head chd) on the CUDA cores: lane = key for the scores, lane = dim for P*V
+                uint4 qv[4];                                                // the class token's q row for (cimg, head): 32 values
+                if (cimg < p.B) {
+                    const uint4* qg = reinterpret_cast<const uint4*>(p.qkv_cls + static_cast<size_t>(cimg) * 3 * p.C + hg * 64 + chd * 32);
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) qv[c] = __ldg(qg + c);
+                }
+                mbar_wait(ready_bar, hg_it & 1u);
+                if (q == 0) qa_stamp(p, 1, hg_it, 3);
+                if (cimg < p.B) {
+                    const uint8_t* Kt = smem_k + cj * QA_REG;
+                    const uint8_t* Vt = smem_v + cj * QA_REG;
+                    float sc[3];
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) {
+                        const int key = lane + 32 * i;
+                        float a = -INFINITY;
+                        if (key < QA_L) {
+                            a = 0.f;
+                            const uint8_t* row = Kt + key * 128;
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) {
+                                const uint4 kv = *reinterpret_cast<const uint4*>(row + (((chd * 4 + c) ^ (key & 7)) << 4));
+                                const uint32_t kw[4] = {kv.x, kv.y, kv.z, kv.w};
+                                const uint32_t qw[4] = {qv[c].x, qv[c].y, qv[c].z, qv[c].w};
+#pragma unroll
+                                for (int w = 0; w < 4; ++w) {
+                                    const float2 a2 = unpack2<F16>(qw[w]), b2 = unpack2<F16>(kw[w]);
+                                    a = fmaf(a2.x, b2.x, a);
+                                    a = fmaf(a2.y, b2.y, a);
+                                }
+                            }
+                            a *= p.scale_log2e;
+                        }
+                        sc[i] = a;
+                    }
+                    float m = fmaxf(sc[0], fmaxf(sc[1], sc[2]));
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+                    float e[3], sum = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) { e[i] = ex2_approx(sc[i] - m); sum += e[i]; }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                    float ov = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) {
+#pragma unroll
+                        for (int src = 0; src < 32; ++src) {
+                            const int key = src + 32 * i;
+                            if (key < QA_L) {
+                                const float pk = __shfl_sync(0xffffffffu, e[i], src);
+                                const uint16_t hv = *reinterpret_cast<const uint16_t*>(Vt + key * 128 + ((vch ^ (key & 7)) << 4) + voff);
+                                ov = fmaf(pk, unpack1<F16>(hv), ov);
+                            }
+                        }
+                    }
+                    ov *= __frcp_rn(sum);
+                    reinterpret_cast<uint16_t*>(p.out)[static_cast<size_t>(cimg) * QA_L * p.C + hg * 64 + chd * 32 + lane] =
+                        static_cast<uint16_t>(pack2<F16>(ov, 0.f) & 0xffffu);
+                }
+                __syncwarp();
+                if (q == 0) qa_stamp(p, 1, hg_it, 4);
+                if (lane == 0) mbar_arrive(free_bar);
             }
         }
     } else if (warp >= 8) {
-        // ================================================================= attention (warps 8-17) and class rows (18-19)
+        // ================================================================= attention: task = (image j, 16 patch rows, head)
         const int aw = warp - 8;
+        const int j = aw >> 3, q0 = ((aw >> 1) & 3) * 16, cbase = (aw & 1) * 4;
         const int g = lane >> 2, t = lane & 3;
+        uint8_t* Qt = smem_q + j * QA_REG;
+        const uint8_t* Kt = smem_k + j * QA_REG;
+        const uint8_t* Vt = smem_v + j * QA_REG;
         uint32_t hg_it = 0;
         for (int tp = first_tp; tp < p.num_tp; tp += tp_step) {
+            const int img = image_of(tp, j);
             for (int hg = 0; hg < p.n_hg; ++hg, ++hg_it) {
-                if (aw >= 10) {
-                    // class row of image aw - 10: q | k | v of this head pair from the class-row GEMM -> row 64 of the tiles
-                    const int j = aw - 10, img = image_of(tp, j);
-                    if (hg_it > 0) mbar_wait(free_bar, (hg_it - 1) & 1u);
-                    if (lane < 24 && img < p.B) {
-                        const int s = lane >> 3, ch = lane & 7;
-                        const uint4 val = __ldg(reinterpret_cast<const uint4*>(p.qkv_cls + static_cast<size_t>(img) * 3 * p.C + s * p.C + hg * 64) + ch);
-                        uint8_t* base = (s == 0 ? smem_q : (s == 1 ? smem_k : smem_v)) + j * QA_REG;
-                        *reinterpret_cast<uint4*>(base + 64 * 128 + (ch << 4)) = val;         // row 64: swizzle term (64 & 7) = 0
-                    }
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(ready_bar);
-                    continue;
-                }
-                // task = (image j, query tile qt): both heads of the pair
-                const int j = aw / 5, qt = aw % 5, q0 = qt * 16;
-                const int img = image_of(tp, j);
                 mbar_wait(ready_bar, hg_it & 1u);
-                uint8_t* Qt = smem_q + j * QA_REG;
-                const uint8_t* Kt = smem_k + j * QA_REG;
-                const uint8_t* Vt = smem_v + j * QA_REG;
+                if (aw == 0) qa_stamp(p, 2, hg_it, 0);
                 if (img < p.B) {
+                    uint32_t qa[2][4];
 #pragma unroll
-                    for (int head = 0; head < 2; ++head) {
-                        const int cbase = head * 4;
-                        uint32_t qa[2][4];
+                    for (int ks = 0; ks < 2; ++ks) {
+                        const int qrow = q0 + (lane & 7) + (((lane >> 3) & 1) << 3);
+                        ldmatrix_x4(qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], att_addr<true>(Qt, qrow, cbase + ks * 2 + (lane >> 4), 0));
+                    }
+                    float o[4][4];
+                    attend_qtile<32, 80, F16, true, 128, true>(qa, Kt, Vt, QA_L, 80, p.scale_log2e, lane, o, cbase);
+                    if (aw == 0) qa_stamp(p, 2, hg_it, 1);
+                    __syncwarp();                                 // all lanes have their Q fragments: reuse those columns as stage
 #pragma unroll
-                        for (int ks = 0; ks < 2; ++ks) {
-                            const int qrow = q0 + (lane & 7) + (((lane >> 3) & 1) << 3);
-                            ldmatrix_x4(qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3], att_addr<true>(Qt, qrow, cbase + ks * 2 + (lane >> 4), 0));
-                        }
-                        float o[4][4];
-                        attend_qtile<32, 80, F16, true, 128, true>(qa, Kt, Vt, QA_L, 80, p.scale_log2e, lane, o, cbase);
-                        __syncwarp();                             // all lanes have their Q fragments: reuse the patch as stage
-#pragma unroll
-                        for (int dt = 0; dt < 4; ++dt) {
-                            const int r0 = q0 + g, r1 = q0 + g + 8;
-                            *reinterpret_cast<uint32_t*>(Qt + r0 * 128 + (((cbase + dt) ^ (r0 & 7)) << 4) + 4 * t) = pack2<F16>(o[dt][0], o[dt][1]);
-                            *reinterpret_cast<uint32_t*>(Qt + r1 * 128 + (((cbase + dt) ^ (r1 & 7)) << 4) + 4 * t) = pack2<F16>(o[dt][2], o[dt][3]);
-                        }
+                    for (int dt = 0; dt < 4; ++dt) {
+                        const int r0 = q0 + g, r1 = q0 + g + 8;
+                        *reinterpret_cast<uint32_t*>(Qt + r0 * 128 + (((cbase + dt) ^ (r0 & 7)) << 4) + 4 * t) = pack2<F16>(o[dt][0], o[dt][1]);
+                        *reinterpret_cast<uint32_t*>(Qt + r1 * 128 + (((cbase + dt) ^ (r1 & 7)) << 4) + 4 * t) = pack2<F16>(o[dt][2], o[dt][3]);
                     }
                     __syncwarp();
-                    // this warp's 16 rows x 128 B -> global; local row r < 64 is token 1 + r, local row 64 the class token 0
-                    bf16* ob = p.out + static_cast<size_t>(img) * QA_L * p.C + hg * 64;
+                    // this warp's 16 rows x 64 B -> global; local row r is token 1 + r
+                    bf16* ob = p.out + static_cast<size_t>(img) * QA_L * p.C + hg * 64 + (aw & 1) * 32;
 #pragma unroll
-                    for (int i = lane; i < 16 * 8; i += 32) {
-                        const int r = q0 + (i >> 3), ch = i & 7;
-                        if (r <= 64) {
-                            const int token = r < 64 ? r + 1 : 0;
-                            *reinterpret_cast<uint4*>(ob + static_cast<size_t>(token) * p.C + ch * 8) =
-                                *reinterpret_cast<const uint4*>(Qt + r * 128 + ((ch ^ (r & 7)) << 4));
-                        }
+                    for (int i = lane; i < 16 * 4; i += 32) {
+                        const int r = q0 + (i >> 2), ch = i & 3;
+                        *reinterpret_cast<uint4*>(ob + static_cast<size_t>(r + 1) * p.C + ch * 8) =
+                            *reinterpret_cast<const uint4*>(Qt + r * 128 + (((cbase + ch) ^ (r & 7)) << 4));
                     }
                 }
                 __syncwarp();
+                if (aw == 0) qa_stamp(p, 2, hg_it, 2);
                 if (lane == 0) mbar_arrive(free_bar);
             }
         }
