@@ -72,6 +72,26 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// The same wait with a suspend-time hint: the hardware parks the thread until the phase completes (or the hint, in
+// nanoseconds, runs out) instead of returning at once, so a waiting warp does not compete for issue slots with the
+// warps that work.  For kernels in which many warps of an SM wait on each other most of the time.
+__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity) {
+    uint32_t spins = 0, ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.b32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity), "r"(20000u)
+            : "memory");
+        if (!ok && ++spins > (DDC_SPIN_LIMIT >> 6)) {
+            printf("ddimcold: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+            __trap();
+        }
+    } while (!ok);
+}
+
 // ----------------------------------------------------------------------------- proxies / fences
 __device__ __forceinline__ void fence_proxy_async_smem() {
     // generic-proxy smem writes -> visible to the async proxy (TMA / tcgen05.mma operand reads)
@@ -383,6 +403,12 @@ __device__ __forceinline__ void tmem_ld_wait(float* v) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
     for (int i = 0; i < 128; i += 8)
+        asm volatile("" : "+f"(v[i]), "+f"(v[i + 1]), "+f"(v[i + 2]), "+f"(v[i + 3]), "+f"(v[i + 4]), "+f"(v[i + 5]), "+f"(v[i + 6]), "+f"(v[i + 7]));
+}
+__device__ __forceinline__ void tmem_ld_wait32(float* v) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; i += 8)
         asm volatile("" : "+f"(v[i]), "+f"(v[i + 1]), "+f"(v[i + 2]), "+f"(v[i + 3]), "+f"(v[i + 4]), "+f"(v[i + 5]), "+f"(v[i + 6]), "+f"(v[i + 7]));
 }
 __device__ __forceinline__ void tmem_ld_wait64(float* v) {

@@ -19,6 +19,7 @@
 #include "attention_fa.cuh"
 #include "fp32_path.cuh"
 #include "qkv_attn.cuh"
+#include "qkv_attn_tc.cuh"
 
 using namespace ddc;
 
@@ -353,12 +354,17 @@ static int launch_qkv_attn(const CUtensorMap& tmA, const CUtensorMap& tmW, QkvAt
     static int attr_dev_mask = 0;
     int dev = 0;
     CK(cudaGetDevice(&dev));
-    auto kern = qkv_attn_kernel<F16>;
+    auto kern_ws = qkv_attn_kernel<F16>;
     if (!(attr_dev_mask & (1 << dev))) {
-        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CK(cudaFuncSetAttribute(qkv_attn_tc_kernel<F16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CK(cudaFuncSetAttribute(qkv_attn_tc_kernel<F16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CK(cudaFuncSetAttribute(kern_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_dev_mask |= (1 << dev);
     }
-    int stages = static_cast<int>((227 * 1024 - static_cast<long>(qkv_attn_smem_bytes(p.C, 0))) / (96 * 128));
+    // DDC_QKV_ATTN: 1 (default) = attention on tcgen05 too; 2 = warp-level mma.sync attention inside the fused kernel
+    const bool tc = env_int("DDC_QKV_ATTN", 1) != 2;
+    const size_t fixed = tc ? qkv_attn_tc_smem_bytes(p.C, 0) : qkv_attn_smem_bytes(p.C, 0);
+    int stages = static_cast<int>((227 * 1024 - static_cast<long>(fixed)) / (96 * 128));
     if (stages > 8) stages = 8;
     if (stages < 2) return fail(DDC_E_INVALID, "qkv+attention: C=%d leaves no room for the weight ring", p.C);
     p.stages = stages;
@@ -366,9 +372,13 @@ static int launch_qkv_attn(const CUtensorMap& tmA, const CUtensorMap& tmW, QkvAt
     p.num_tp = (p.B + 3) / 4;
     p.scale_log2e = (1.0f / sqrtf(32.0f)) * 1.44269504088896340736f;
     p.trace = g_qa_trace;
-    int grid = 2 * p.num_tp < num_sms() ? 2 * p.num_tp : num_sms();
+    p.n_split = (tc && p.n_hg % 2 == 0) ? 2 : 1;
+    const int units = p.num_tp * p.n_split;
+    int grid = 2 * units < num_sms() ? 2 * units : num_sms();
     grid = grid / 2 * 2;
-    CK(launch_chain(kern, dim3(grid), dim3(QA_THREADS), qkv_attn_smem_bytes(p.C, stages), st, 2, tmA, tmW, p));
+    if (tc && g_qa_trace) CK(launch_chain(qkv_attn_tc_kernel<F16, true>, dim3(grid), dim3(QT_THREADS), qkv_attn_tc_smem_bytes(p.C, stages), st, 2, tmA, tmW, p));
+    else if (tc) CK(launch_chain(qkv_attn_tc_kernel<F16, false>, dim3(grid), dim3(QT_THREADS), qkv_attn_tc_smem_bytes(p.C, stages), st, 2, tmA, tmW, p));
+    else CK(launch_chain(kern_ws, dim3(grid), dim3(QA_THREADS), qkv_attn_smem_bytes(p.C, stages), st, 2, tmA, tmW, p));
     return DDC_OK;
 }
 

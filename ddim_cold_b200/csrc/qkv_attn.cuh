@@ -30,11 +30,12 @@ constexpr int QA_L = 65;
 
 struct QkvAttnParams {
     int B, C, n_hg, stages, num_tp;   // images, embed_dim, head pairs, W ring stages, tile pairs (4 images each)
+    int n_split;                      // work units per tile pair (tcgen05 version): the head pairs are cut into this many runs
     const float* bias_hp;             // [n_hg][192] bias in the rearranged order
     const bf16* qkv_cls;              // [B, 3C] q | k | v of the class rows (standard column order)
     bf16* out;                        // [B * 65, C]
     float scale_log2e;
-    long long* trace;                 // optional [4 roles][32 head-pair iterations][8 events] clock stamps of CTA 0 (tuning aid)
+    long long* trace;                 // optional [6 roles][32 head-pair iterations][8 events] clock stamps of CTA 0 (tuning aid)
 };
 
 __device__ __forceinline__ void qa_stamp(const QkvAttnParams& p, int role, uint32_t it, int ev) {

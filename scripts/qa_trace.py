@@ -25,7 +25,7 @@ b = torch.randn(3 * Cd, device="cuda") * 0.2
 out = torch.zeros(M, Cd, device="cuda", dtype=torch.float16)
 w_hp, b_hp = torch.empty_like(W), torch.empty_like(b)
 cls = torch.empty(B, 3 * Cd, device="cuda", dtype=torch.float16)
-trace = torch.zeros(4 * 32 * 8, device="cuda", dtype=torch.int64)
+trace = torch.zeros(6 * 32 * 8, device="cuda", dtype=torch.int64)
 st = torch.cuda.current_stream().cuda_stream
 lib.ddc_dbg_qkv_attn_trace.argtypes = [C.c_void_p]
 
@@ -42,14 +42,20 @@ lib.ddc_dbg_qkv_attn_trace(C.c_void_p(trace.data_ptr()))
 run()
 torch.cuda.synchronize()
 lib.ddc_dbg_qkv_attn_trace(C.c_void_p(0))
-t = trace.cpu().reshape(4, 32, 8)
+t = trace.cpu().reshape(6, 32, 8)
 t0 = int(t[t > 0].min())
-names = {0: ["mma:acc free", "mma:first W", "mma:issued"], 1: ["epi:acc full", "epi:tiles free", "epi:drained", "epi:ready", "epi:cls done"],
-         2: ["att:ready", "att:attended", "att:stored"]}
+if os.environ.get("DDC_QKV_ATTN", "1") == "2":        # warp-level attention inside the fused kernel
+    names = {0: ["mma:acc free", "mma:first W", "mma:issued"], 1: ["epi:acc full", "epi:tiles free", "epi:drained", "epi:ready", "epi:cls done"],
+             2: ["att:ready", "att:attended", "att:stored"]}
+else:                                                  # tcgen05 attention
+    names = {0: ["mma:acc free", "mma:first W", "mma:issued"], 1: ["epi:acc full", "epi:tiles free", "epi:drained", "epi:q", "epi:k", "epi:v"],
+             4: ["cls:tiles free", "cls:qkv ready", "cls:done"],
+             3: ["-", "S issued"],
+             2: ["smx:S full", "smx:P written", "smx:O full", "smx:stored"]}
 n_it = 2 * (Cd // 64) + 2
 for it in range(n_it):
     parts = []
-    for role in (0, 1, 2):
+    for role in names:
         for ev, nm in enumerate(names[role]):
             v = int(t[role, it, ev])
             parts.append(f"{nm}={v - t0 if v else -1}")
