@@ -3,6 +3,7 @@
 from .vit import DiffusionVisionTransformer
 from .checkpoint import infer_shape, load_checkpoint, model_from_yaml
 from .shard import SharedHostImages, shard_bounds, sample_sharded
+from .evaluate import evaluate, smooth_l1_loss
 
 __all__ = ["DiffusionVisionTransformer", "infer_shape", "load_checkpoint", "model_from_yaml",
-           "shard_bounds", "sample_sharded", "SharedHostImages"]
+           "shard_bounds", "sample_sharded", "SharedHostImages", "evaluate", "smooth_l1_loss"]

@@ -60,6 +60,7 @@ SIGNATURES = {
     "ddc_k_qkv_attn": (C.c_int, [_i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "ddc_k_patchify": (C.c_int, [_i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
     "ddc_k_affine": (C.c_int, [_vp, _vp, _sz, C.c_float, C.c_float, _vp]),
+    "ddc_k_smooth_l1": (C.c_int, [_vp, _vp, _sz, _vp, _vp, _vp]),
     "ddc_k_mix": (C.c_int, [_vp, _vp, _vp, _sz, _sz, C.c_float, C.c_float, _vp]),
     "ddc_k_head_ddim": (C.c_int, [_vp, _i32, _vp, _i32, _i32, _i32, _i32, C.POINTER(Step), _vp, _vp, _vp]),
 }

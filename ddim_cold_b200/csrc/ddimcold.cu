@@ -1366,6 +1366,20 @@ extern "C" int ddc_k_patchify(int32_t fmt, const float* x, void* ap, int32_t bat
     return DDC_OK;
 }
 
+extern "C" int ddc_k_smooth_l1(const float* pred, const float* target, size_t n, float* scratch, float* out, void* stream) {
+    if (pred == nullptr || target == nullptr || scratch == nullptr || out == nullptr) return fail(DDC_E_INVALID, "NULL tensor");
+    if ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(target)) & 15) return fail(DDC_E_INVALID, "smooth_l1: 16-byte alignment");
+    if (n == 0) return fail(DDC_E_INVALID, "smooth_l1: empty tensors (the reference's mean over nothing is NaN)");
+    size_t blocks = (n / 4 + 255) / 256;
+    const size_t cap = static_cast<size_t>(num_sms()) * 4;          // <= 1023 block sums fit the scratch
+    if (blocks > cap) blocks = cap;
+    if (blocks > 1023) blocks = 1023;
+    if (blocks == 0) blocks = 1;
+    smooth_l1_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(pred, target, n, scratch, out);
+    CK(cudaGetLastError());
+    return DDC_OK;
+}
+
 extern "C" int ddc_k_affine(const float* in, float* out, size_t n, float add, float mul, void* stream) {
     if (in == nullptr || out == nullptr) return fail(DDC_E_INVALID, "NULL tensor");
     if ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) return fail(DDC_E_INVALID, "affine: 16-byte alignment");

@@ -346,6 +346,51 @@ __global__ void __launch_bounds__(256) mix_kernel(const float* __restrict__ z, c
         out[i] = __fadd_rn(__fmul_rn(z[i], a), __fmul_rn(draft[i % period], b));
 }
 
+// mean over n elements of smooth_l1(pred - target) with beta = 1 (F.smooth_l1_loss defaults; the trainer's evaluate(),
+// multi_gpu_trainer.py:42): 0.5 d^2 for |d| < 1, |d| - 0.5 otherwise.  One pass over both tensors (float4 lanes), a
+// block sum per CTA into scratch[0 .. gridDim.x), and the CTA that finishes last adds the block sums in index order in
+// double precision -- the result does not depend on the order in which CTAs finish.  scratch[1023] is the ticket
+// counter: zero before the first call, left at zero by every call.
+__global__ void __launch_bounds__(256) smooth_l1_kernel(const float* __restrict__ pred, const float* __restrict__ target, size_t n,
+                                                        float* __restrict__ scratch, float* __restrict__ out) {
+    const size_t n4 = n >> 2;
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    auto term = [](float a, float b) {
+        const float d = fabsf(a - b);
+        return d < 1.f ? 0.5f * d * d : d - 0.5f;
+    };
+    float acc = 0.f;
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+        const float4 a = reinterpret_cast<const float4*>(pred)[i], b = reinterpret_cast<const float4*>(target)[i];
+        acc += (term(a.x, b.x) + term(a.y, b.y)) + (term(a.z, b.z) + term(a.w, b.w));
+    }
+    for (size_t i = (n4 << 2) + blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n; i += stride)
+        acc += term(pred[i], target[i]);
+    __shared__ float warp_sum[8];
+    __shared__ bool last;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float b = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) b += warp_sum[w];
+        scratch[blockIdx.x] = b;
+        __threadfence();
+        unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + 1023);
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last && threadIdx.x == 0) {
+        __threadfence();
+        double t = 0.0;
+        for (unsigned int i = 0; i < gridDim.x; ++i) t += static_cast<double>(reinterpret_cast<volatile float*>(scratch)[i]);
+        out[0] = static_cast<float>(t / static_cast<double>(n));
+        *reinterpret_cast<unsigned int*>(scratch + 1023) = 0u;
+    }
+}
+
 __global__ void copy_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, size_t n) {
     for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
          i += static_cast<size_t>(gridDim.x) * blockDim.x)

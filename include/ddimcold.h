@@ -214,6 +214,13 @@ int ddc_k_patchify(int32_t fmt, const float* x, void* ap, int32_t batch, int32_t
 int ddc_k_head_ddim(const float* y, int32_t ldy, float* x, int32_t batch, int32_t H, int32_t W, int32_t patch,
                     const ddc_step* host_step, float* x0_out, float* eps_out, void* stream);
 
+/* out[0] = mean_i smooth_l1(pred[i] - target[i]) with beta = 1 -- F.smooth_l1_loss(denoised_img, img) of the trainer's
+ * evaluate() (reference multi_gpu_trainer.py:42), so that a validation pass stays on the device.  pred, target: fp32,
+ * 16-byte aligned, n > 0 elements.  scratch: 1024 floats of device memory, ZERO before the first call (the last one is a
+ * ticket counter that every call leaves at zero again); calls that share a scratch must not overlap.  The sum is formed
+ * in a fixed order (block sums in index order, in double), so the value is reproducible run to run. */
+int ddc_k_smooth_l1(const float* pred, const float* target, size_t n, float* scratch, float* out, void* stream);
+
 /* out[i] = (in[i] + add) * mul over n floats (16-byte aligned pointers; in == out allowed).  The samplers' return
  * value is (x0 + 1) / 2 (reference ViT.py:237, ViT_draft2drawing.py:288): applied on the device before the copy back. */
 int ddc_k_affine(const float* in, float* out, size_t n, float add, float mul, void* stream);

@@ -245,3 +245,25 @@ def d2d(sd, sh: Shape, noise, draft, t_start: int, k: int = 10, dtype=np.float32
     x = d2d_init(np.asarray(noise, dtype=dtype), np.asarray(draft, dtype=dtype), t_start, sh.total_steps)
     x0, _ = denoise_loop(sd, sh, x.astype(dtype), k, t_start=t_start, dtype=dtype)
     return (x0 + 1) / 2
+
+
+def synth_eval_batches(sh, n_batches=3, batch=6):
+    """Synthetic (noisy_img, img, t) batches for the trainer-side evaluate() fixture (multi_gpu_trainer.py:36):
+    images in [-1, 1], noised to the sqrt-schedule level of their own t; travels as seeds."""
+    out = []
+    for i in range(n_batches):
+        img = np.clip(synth_noise((batch, 3, sh.img_h, sh.img_w), seed=400 + i) * 0.6, -1, 1).astype(np.float32)
+        noise = synth_noise((batch, 3, sh.img_h, sh.img_w), seed=500 + i)
+        t = (np.arange(batch) * 397 + 131 * i + 5) % sh.total_steps
+        alpha = (1 - np.sqrt((t + 1) / sh.total_steps)).astype(np.float32)[:, None, None, None]
+        noisy = (np.sqrt(alpha) * img + np.sqrt(1 - alpha) * noise).astype(np.float32)
+        out.append((noisy, img, t.astype(np.int64)))
+    return out
+
+
+
+def smooth_l1_mean(pred, target):
+    """F.smooth_l1_loss(pred, target) with its defaults (beta = 1, mean), in float64 (multi_gpu_trainer.py:42)."""
+    d = np.abs(np.asarray(pred, dtype=np.float64) - np.asarray(target, dtype=np.float64))
+    return float(np.where(d < 1, 0.5 * d * d, d - 0.5).mean())
+

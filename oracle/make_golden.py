@@ -288,7 +288,43 @@ def gen_fused(ViT, D2D, record):
     np.savez_compressed(os.path.join(OUT, "fused.npz"), **fix)
 
 
-CASES = {"tiny": gen_tiny, "real": gen_real, "s3": gen_s3, "fused": gen_fused}
+def reference_evaluate():
+    """The reference's `evaluate` (multi_gpu_trainer.py:32-45) executed from its own source text: the module itself
+    cannot be imported here (it pulls in torchvision / tensorboard / a dataset path at import time)."""
+    import torch.nn.functional as F
+    with open(os.path.join(REF, "multi_gpu_trainer.py")) as f:
+        src = f.read()
+    a = src.index("def evaluate(")
+    b = src.index("def main(", a)
+    ns = {"torch": torch, "np": np, "F": F}
+    exec(compile(src[a:b], "multi_gpu_trainer.py:evaluate", "exec"), ns)
+    return ns["evaluate"]
+
+
+def gen_evaluate(ViT, D2D, record):
+    # ------------------------------------------------------------------ trainer-side evaluate() on the fused-path shape
+    sh = O.Shape(32, 32, 4, 128, 2, 4)
+    sd = O.synth_state_dict(sh, seed=3, rich=True, gain=2.0)
+    md = ref_model(D2D, sh, sd)                       # the trainer builds the ViT_draft2drawing class
+    ev = reference_evaluate()
+    batches = [tuple(torch.from_numpy(a) for a in b) for b in O.synth_eval_batches(sh)]
+    mean = ev(md, batches, "cpu")
+    per_batch = []
+    import torch.nn.functional as F
+    with torch.no_grad():
+        for noisy, img, t in batches:
+            per_batch.append(float(F.smooth_l1_loss(md(noisy, t), img)))
+    assert abs(np.array(per_batch).mean() - mean) < 1e-12
+    # the oracle's forward + a float64 smooth-L1 against the reference's numbers
+    ol = []
+    for noisy, img, t in O.synth_eval_batches(sh):
+        d = np.abs(O.forward(sd, sh, noisy, t, np.float32).astype(np.float64) - img)
+        ol.append(np.where(d < 1, 0.5 * d * d, d - 0.5).mean())
+    record("evaluate.loss.np32", maxabs(np.array(ol), np.array(per_batch)))
+    np.savez_compressed(os.path.join(OUT, "evaluate.npz"), mean=np.float64(mean), per_batch=np.array(per_batch, np.float64))
+
+
+CASES = {"tiny": gen_tiny, "real": gen_real, "s3": gen_s3, "fused": gen_fused, "evaluate": gen_evaluate}
 
 
 def main(argv=None):

@@ -156,3 +156,14 @@ def test_s3_forward_and_taps(golden):
     assert maxabs(x0.numpy(), g["tap_x0"][0]) < TOL
     eps, _ = O.ddim_update(g["tap_x_t"][0], g["tap_x0"][0], int(g["tap_t"][0]), 500)
     assert maxabs(eps, g["tap_eps"][0]) < TOL
+
+
+def test_evaluate_fixture_vs_oracle(golden):
+    """Trainer-side evaluate() (multi_gpu_trainer.py:32-45): the per-batch smooth-L1 losses the reference's own function
+    returned for the synthetic batches, against the oracle's forward + a float64 smooth-L1."""
+    g = golden("evaluate")
+    sh = O.Shape(32, 32, 4, 128, 2, 4)
+    sd = O.synth_state_dict(sh, seed=3, rich=True, gain=2.0)
+    losses = [O.smooth_l1_mean(O.forward(sd, sh, noisy, t, np.float32), img) for noisy, img, t in O.synth_eval_batches(sh)]
+    assert np.abs(np.array(losses) - g["per_batch"]).max() < 1e-6
+    assert abs(np.mean(losses) - float(g["mean"])) < 1e-6
