@@ -372,7 +372,21 @@ static int launch_qkv_attn(const CUtensorMap& tmA, const CUtensorMap& tmW, QkvAt
     p.num_tp = (p.B + 3) / 4;
     p.scale_log2e = (1.0f / sqrtf(32.0f)) * 1.44269504088896340736f;
     p.trace = g_qa_trace;
-    p.n_split = (tc && p.n_hg % 2 == 0) ? 2 : 1;
+    // Work units per 4-image tile: the tile's head pairs are cut into n_split runs, each run a unit of its own (it reloads
+    // the tile's activations, ~0.4 head-pair times).  More, shorter units shorten the last round of a large grid and
+    // spread a small batch over more SMs; the result of an (image, head) does not depend on the cut.  Picked by cost:
+    // rounds * (head pairs per unit + reload).
+    p.n_split = 1;
+    if (tc) {
+        const int pairs = num_sms() / 2;
+        float best = 1e30f;
+        for (int d = 1; d <= p.n_hg; ++d) {
+            if (p.n_hg % d) continue;
+            const int rounds = (p.num_tp * d + pairs - 1) / pairs;
+            const float cost = static_cast<float>(rounds) * (static_cast<float>(p.n_hg / d) + 0.4f);
+            if (cost < best - 1e-3f) { best = cost; p.n_split = d; }
+        }
+    }
     const int units = p.num_tp * p.n_split;
     int grid = 2 * units < num_sms() ? 2 * units : num_sms();
     grid = grid / 2 * 2;

@@ -146,7 +146,7 @@ qkv_attn_tc_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C]
     // Accumulator -> Q / K / V tiles: three 32-column chunks starting at chunk c0 (q = chunks 0-1, k = 2-3, v = 4-5) of
     // the calling warp's TMEM lane quarter.  The epilogue warps take chunks 0-2, the class-row warps (idle at that
     // time, same lane quarters) chunks 3-5.  One rolled loop: straight-line code runs at instruction-fetch speed here.
-    auto drain3 = [&](int c0, int hg) {
+    auto drain3 = [&](int c0, int hg, uint32_t trace_it) {
         const int q = warp & 3, r = q * 32 + lane;
         const uint32_t lane_taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
         const float* bias = smem_bias + hg * QA_NB;
@@ -168,6 +168,7 @@ qkv_attn_tc_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C]
                 w.w = pack2<F16>(v[8 * j + 6] + b1.z, v[8 * j + 7] + b1.w);
                 *reinterpret_cast<uint4*>(row + (((half + j) ^ (r & 7)) << 4)) = w;
             }
+            if constexpr (TRACE) { if (q == 0) qa_stamp(p, c0 == 0 ? 1 : 4, trace_it, 3 + c - c0); }
         }
         fence_proxy_async_smem();                                   // the tiles (and the class keys) are MMA operands
         tc_fence_before();
@@ -271,7 +272,7 @@ qkv_attn_tc_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C]
                 if constexpr (TRACE) { if (q == 0) qa_stamp(p, 1, it, 0); }
                 if (it > 0) mbar_wait_parked(qkv_free, (it - 1) & 1u);
                 if constexpr (TRACE) { if (q == 0) qa_stamp(p, 1, it, 1); }
-                drain3(0, hg);
+                drain3(0, hg, it);
                 if (q == 0) {
                     issue_s(it);
                     if constexpr (TRACE) { qa_stamp(p, 3, it, 1); }
@@ -423,7 +424,7 @@ qkv_attn_tc_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C]
                 if (lane == 0) mbar_arrive(cls_ready);
                 mbar_wait_parked(tfull_bar, par);                           // second half of the accumulator drain
                 tc_fence_after();
-                drain3(3, hg);
+                drain3(3, hg, it);
                 float scl = qf * kf;                                        // class query x class key
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) scl += __shfl_xor_sync(0xffffffffu, scl, o);

@@ -48,8 +48,8 @@ if os.environ.get("DDC_QKV_ATTN", "1") == "2":        # warp-level attention ins
     names = {0: ["mma:acc free", "mma:first W", "mma:issued"], 1: ["epi:acc full", "epi:tiles free", "epi:drained", "epi:ready", "epi:cls done"],
              2: ["att:ready", "att:attended", "att:stored"]}
 else:                                                  # tcgen05 attention
-    names = {0: ["mma:acc free", "mma:first W", "mma:issued"], 1: ["epi:acc full", "epi:tiles free", "epi:drained", "epi:q", "epi:k", "epi:v"],
-             4: ["cls:tiles free", "cls:qkv ready", "cls:done"],
+    names = {0: ["mma:acc free", "mma:first W", "mma:issued"], 1: ["epi:acc full", "epi:tiles free", "epi:drained", "epi:c0", "epi:c1", "epi:c2"],
+             4: ["cls:tiles free", "cls:drained", "cls:done", "cls:c3", "cls:c4", "cls:c5"],
              3: ["-", "S issued"],
              2: ["smx:S full", "smx:P written", "smx:O full", "smx:stored"]}
 n_it = 2 * (Cd // 64) + 2
