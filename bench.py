@@ -322,6 +322,12 @@ class Leg:
         names = list(CLASS_NAMES)
         if fused_tail:
             names[4] = "block_tail(proj+ln+fc1+gelu+fc2+ln)"
+        fused_qa = bool(self.lib.ddc_plan_fused_qkv_attention(self.plan.handle))
+        if fused_qa:      # class 2 = qkv of the class rows only, class 3 = qkv GEMM of the patch rows + attention in one kernel
+            names[2], names[3] = "cls_row_qkv_gemm", "qkv_attention_fused"
+            n_patch = L - 1
+            cls_flops[2] = 2.0 * B * 3 * Cdim * Cdim
+            cls_flops[3] = 2.0 * B * n_patch * 3 * Cdim * Cdim + 4.0 * B * L * L * Cdim
         kernels = {}
         step_ms_sum = sum(cls_ms[i] for i in range(9)) / prof_steps
         for i, name in enumerate(names):
@@ -334,10 +340,11 @@ class Leg:
         dom = max((i for i in (2, 3, 4) if cls_n[i]), key=lambda i: cls_ms[i])
         dom_ms = cls_ms[dom] / cls_n[dom]
         dom_name = {2: "gemm2_kernel<S_BF16> (LN-fed qkv GEMM, tcgen05 cta_group::2)",
-                    3: "attention kernel (softmax(QK^T)V per image and head)",
+                    3: "qkv_attn_tc_kernel (LN-fed qkv GEMM + attention in one kernel, tcgen05 cta_group::2 + ::1)" if fused_qa
+                       else "attention kernel (softmax(QK^T)V per image and head)",
                     4: "block_tail_kernel (proj + LN2 + fc1 + GELU + fc2 + LN, tcgen05 cta_group::2)" if fused_tail
                        else "gemm2_kernel<R_RESID> (proj GEMM + residual + LN)"}[dom]
-        dom_cls = {2: "qkv", 3: "attention", 4: "block_tail" if fused_tail else "proj"}[dom]
+        dom_cls = {2: "qkv", 3: "qkv_attention" if fused_qa else "attention", 4: "block_tail" if fused_tail else "proj"}[dom]
         return kernels, {"name": dom_name, "cls": dom_cls, "ms": dom_ms, "flops": cls_flops[dom],
                          "share": (cls_ms[dom] / prof_steps) / step_ms_sum}
 

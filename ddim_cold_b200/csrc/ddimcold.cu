@@ -354,17 +354,12 @@ static int launch_qkv_attn(const CUtensorMap& tmA, const CUtensorMap& tmW, QkvAt
     static int attr_dev_mask = 0;
     int dev = 0;
     CK(cudaGetDevice(&dev));
-    auto kern_ws = qkv_attn_kernel<F16>;
     if (!(attr_dev_mask & (1 << dev))) {
         CK(cudaFuncSetAttribute(qkv_attn_tc_kernel<F16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         CK(cudaFuncSetAttribute(qkv_attn_tc_kernel<F16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        CK(cudaFuncSetAttribute(kern_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_dev_mask |= (1 << dev);
     }
-    // DDC_QKV_ATTN: 1 (default) = attention on tcgen05 too; 2 = warp-level mma.sync attention inside the fused kernel
-    const bool tc = env_int("DDC_QKV_ATTN", 1) != 2;
-    const size_t fixed = tc ? qkv_attn_tc_smem_bytes(p.C, 0) : qkv_attn_smem_bytes(p.C, 0);
-    int stages = static_cast<int>((227 * 1024 - static_cast<long>(fixed)) / (96 * 128));
+    int stages = static_cast<int>((227 * 1024 - static_cast<long>(qkv_attn_tc_smem_bytes(p.C, 0))) / (96 * 128));
     if (stages > 8) stages = 8;
     if (stages < 2) return fail(DDC_E_INVALID, "qkv+attention: C=%d leaves no room for the weight ring", p.C);
     p.stages = stages;
@@ -377,22 +372,20 @@ static int launch_qkv_attn(const CUtensorMap& tmA, const CUtensorMap& tmW, QkvAt
     // spread a small batch over more SMs; the result of an (image, head) does not depend on the cut.  Picked by cost:
     // rounds * (head pairs per unit + reload).
     p.n_split = 1;
-    if (tc) {
-        const int pairs = num_sms() / 2;
-        float best = 1e30f;
-        for (int d = 1; d <= p.n_hg; ++d) {
-            if (p.n_hg % d) continue;
-            const int rounds = (p.num_tp * d + pairs - 1) / pairs;
-            const float cost = static_cast<float>(rounds) * (static_cast<float>(p.n_hg / d) + 0.4f);
-            if (cost < best - 1e-3f) { best = cost; p.n_split = d; }
-        }
+    const int pairs = num_sms() / 2;
+    float best = 1e30f;
+    for (int d = 1; d <= p.n_hg; ++d) {
+        if (p.n_hg % d) continue;
+        const int rounds = (p.num_tp * d + pairs - 1) / pairs;
+        const float cost = static_cast<float>(rounds) * (static_cast<float>(p.n_hg / d) + 0.4f);
+        if (cost < best - 1e-3f) { best = cost; p.n_split = d; }
     }
     const int units = p.num_tp * p.n_split;
     int grid = 2 * units < num_sms() ? 2 * units : num_sms();
     grid = grid / 2 * 2;
-    if (tc && g_qa_trace) CK(launch_chain(qkv_attn_tc_kernel<F16, true>, dim3(grid), dim3(QT_THREADS), qkv_attn_tc_smem_bytes(p.C, stages), st, 2, tmA, tmW, p));
-    else if (tc) CK(launch_chain(qkv_attn_tc_kernel<F16, false>, dim3(grid), dim3(QT_THREADS), qkv_attn_tc_smem_bytes(p.C, stages), st, 2, tmA, tmW, p));
-    else CK(launch_chain(kern_ws, dim3(grid), dim3(QA_THREADS), qkv_attn_smem_bytes(p.C, stages), st, 2, tmA, tmW, p));
+    const size_t smem = qkv_attn_tc_smem_bytes(p.C, stages);
+    if (g_qa_trace) CK(launch_chain(qkv_attn_tc_kernel<F16, true>, dim3(grid), dim3(QT_THREADS), smem, st, 2, tmA, tmW, p));
+    else CK(launch_chain(qkv_attn_tc_kernel<F16, false>, dim3(grid), dim3(QT_THREADS), smem, st, 2, tmA, tmW, p));
     return DDC_OK;
 }
 
@@ -665,6 +658,11 @@ extern "C" int ddc_launches_per_step(const ddc_plan* plan) {
         if (rows_main < plan->L) att = 2;
     }
     return 2 + ((fused ? 2 : 4) + att) * plan->sh.depth + 2;
+}
+
+extern "C" int ddc_plan_fused_qkv_attention(const ddc_plan* plan) {
+    if (plan == nullptr || plan->f32) return 0;
+    return qkv_attn_usable(plan->L, plan->C, plan->sh.heads) ? 1 : 0;
 }
 
 // ------------------------------------------------------------------------------- packing

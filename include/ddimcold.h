@@ -95,6 +95,11 @@ int ddc_plan_set_operand_format(ddc_plan* plan, int32_t fmt);
 /* Largest batch the plan accepts in its current format (max_batch for the 16-bit formats). */
 int ddc_plan_max_batch(const ddc_plan* plan);
 
+/* 1 when this plan's blocks run the qkv Linear and attention as ONE kernel (65-token images with heads of 32 in a
+ * 16-bit operand format; reference ViT.py:105-114), 0 when they run as a qkv GEMM followed by an attention kernel.
+ * For reports: the per-class timings of ddc_profile_steps then mean {class-row qkv GEMM, fused qkv + attention}. */
+int ddc_plan_fused_qkv_attention(const ddc_plan* plan);
+
 /* Pack an fp32 state dict into the plan's weight arena (bf16 K-major GEMM operands, folded
  * cls/pos/conv-bias rows, fp32 time table).  `tensors` is a HOST array of `n_tensors` device
  * pointers in the reference's state_dict order: cls_token, pos_embed, patch_embed.proj.weight,

@@ -87,7 +87,7 @@ with open(f"profiles/{tag}_ncu_full.txt", "w") as f:
         dump(read_raw(path), f)
 
 # ---- traffic of the kernel classes bench.py can name as dominant (S1, 1024 images per GPU): mean over the launches seen
-cls_of = {"block_tail_kernel": "block_tail", "attention_stream_kernel": "attention", "attention_fa_kernel": "attention",
+cls_of = {"block_tail_kernel": "block_tail", "qkv_attn_tc_kernel": "qkv_attention", "attention_stream_kernel": "attention", "attention_fa_kernel": "attention",
           "attention_head_kernel": "attention"}
 traffic = collections.defaultdict(list)
 for d in full:
