@@ -1,7 +1,7 @@
 // Fused tail of a transformer block (ViT.py:136-137 with Mlp.forward :84-90 and the next LayerNorm):
 //
 //     X1 = X + O * Wproj^T + b_proj                       (attention projection + residual)
-//     H  = gelu_erf(LayerNorm2(X1) * Wfc1^T + b_fc1)      (LayerNorm2 folded into fc1, see below)
+//     H  = gelu_erf(LayerNorm2(X1) * Wfc1^T + b_fc1)
 //     X' = X1 + H * Wfc2^T + b_fc2                        (MLP + residual)        -> X  (fp32)
 //     XN = LayerNorm_next(X')                                                      -> XN (16 bit)
 //
@@ -17,17 +17,9 @@
 //          W ring            64-row halves of 128 x 64 weight tiles, gk K blocks per stage, streamed in MMA order
 //
 //   MMA order   proj(n = 0..NB-1) | for j: fc1(j) ; fc2 partial(j): X1[:, n-tile] += H_j * Wfc2[n-tile, j-th K range]
-//   epilogue    epi1: + residual + bias -> TMEM, and the SAME pass writes the 16-bit fc1 operand (X1 - shift) into Abuf
-//               epi2(j): LayerNorm2's row scale / offsets + bias, GELU -> Hbuf[j & 1]
+//   epilogue    epi1: + residual + bias -> TMEM, LayerNorm2 (shifted one-pass statistics, pairwise merge) -> Abuf
+//               epi2(j): + bias, GELU -> Hbuf[j & 1]
 //               epi3: + bias -> X (TMA store), LayerNorm_next -> XN (TMA store)
-//
-// LayerNorm2 is folded into fc1 so that the row block is read from TMEM once, not twice, before the MLP:
-//     fc1(LN2(x1))[o] = rstd * sum_k (x1[k] - s_g(k)) W'[o,k]  +  sum_g rstd (s_g - mean) G_g[o]  +  beff[o]
-// with W' = gamma2 o Wfc1 (16 bit, packed once), s_g the shift of column group g (even / odd 32-column chunks: the
-// first value the group's warps see, so that x1 - s_g is small and keeps its bits in 16-bit), G_g[o] = sum of W'[o,k]
-// over the group's columns (of the ROUNDED W', which is what the tensor core multiplies), beff = beta2 Wfc1^T + b_fc1.
-// The MMA runs on raw shifted activations while the row statistics are still being summed; rstd and the two offsets
-// are per-row scalars applied in the GELU epilogue.
 #pragma once
 
 #include "common.cuh"
@@ -48,9 +40,9 @@ struct BlockTailParams {
     int M, C, stages, num_tiles;
     int gk;                  // K blocks (of 64) per W ring stage: 1 or 2.  One handshake moves gk * 8 KB per CTA.
     const float* b_proj;
-    const float* fc1_g0;     // [C] column sums of the gamma2-scaled fc1 weight over the even 32-column chunks of its K range
-    const float* fc1_g1;     // [C] ... over the odd chunks
-    const float* fc1_beff;   // [C] beta2 * Wfc1^T + b_fc1
+    const float* ln2_g;
+    const float* ln2_b;
+    const float* b_fc1;
     const float* b_fc2;
     const float* lnn_g;      // LayerNorm that follows the block (next block's norm1, or the final norm)
     const float* lnn_b;
@@ -106,7 +98,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     uint64_t* afull_bar = bars + 16;      // [8]  O K block landed              (leader)
     uint64_t* aempty_bar = bars + 24;     // [1]  Abuf no longer read by fc1    (pair commit)
     uint64_t* proj_bar = bars + 25;       // [4]  proj N tile complete          (pair commit)
-    uint64_t* ln2_bar = bars + 56;        // [8]  fc1 operand K block in Abuf   (leader, 8 warps x 2 CTAs)
+    uint64_t* ln2_bar = bars + 56;        // [8]  LayerNorm2 K block in Abuf    (leader, 4 warps x 2 CTAs)
     uint64_t* t1full_bar = bars + 30;     // [1]  fc1 accumulator complete      (pair commit)
     uint64_t* t1free_bar = bars + 31;     // [1]  fc1 accumulator drained       (leader, 16 arrivals)
     uint64_t* hready_bar = bars + 32;     // [2]  hidden block written          (leader, 16 arrivals)
@@ -115,7 +107,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     uint64_t* tfree_bar = bars + 42;      // [4]  N tile of the row block drained by epi3 (leader, 16 arrivals)
     uint64_t* res_bar = bars + 576;       // [4]  residual chunk landed (group x slot), behind the statistics area
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 48);
-    float* red = reinterpret_cast<float*>(bars + 64);     // [3: mean, M2, shift][NG groups][128 rows]
+    float* red = reinterpret_cast<float*>(bars + 64);     // [2 stats][NG groups][128 rows]
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -134,7 +126,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         }
         mbar_init(aempty_bar, 1);
         for (int i = 0; i < 4; ++i) mbar_init(&proj_bar[i], 1);
-        for (int i = 0; i < 8; ++i) mbar_init(&ln2_bar[i], 16);      // a K block = one 32-column chunk of each group x 4 warps x 2 CTAs
+        for (int i = 0; i < 8; ++i) mbar_init(&ln2_bar[i], 8);
         mbar_init(t1full_bar, 1);
         mbar_init(t1free_bar, 8 * NG);              // every epilogue warp of both CTAs
         mbar_init(&hready_bar[0], 8 * NG);
@@ -151,7 +143,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         tmem_relinquish<2>();
     }
     if (warp >= 4) {
-        const float* src[7] = {p.b_proj, p.fc1_g0, p.fc1_g1, p.fc1_beff, p.b_fc2, p.lnn_g, p.lnn_b};
+        const float* src[7] = {p.b_proj, p.ln2_g, p.ln2_b, p.b_fc1, p.b_fc2, p.lnn_g, p.lnn_b};
         for (int i = threadIdx.x - 128; i < 7 * C; i += 128 * NG) sp[i] = src[i / C][i % C];
     }
     tc_fence_before();
@@ -178,9 +170,9 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
     }
     const float* s_bproj = sp;
-    const float* s_fg0 = sp + C;
-    const float* s_fg1 = sp + 2 * C;
-    const float* s_beff = sp + 3 * C;
+    const float* s_g2 = sp + C;
+    const float* s_b2 = sp + 2 * C;
+    const float* s_bfc1 = sp + 3 * C;
     const float* s_bfc2 = sp + 4 * C;
     const float* s_gn = sp + 5 * C;
     const float* s_bn = sp + 6 * C;
@@ -345,14 +337,11 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         // part, and the NG equal-sized parts are merged exactly (Chan et al.): mean = avg(m_i),
         // M2 = sum(M2_i) + n_part * sum((m_i - mean)^2).
         const float part_n = static_cast<float>(C) / static_cast<float>(NG);
-        float* red_shift = red + 2 * NG * 128 + hf * 128 + trow;
-        // off[g] = (shift of group g - mean) * rstd: the per-row offsets of the folded LayerNorm2 (see the head comment)
-        auto row_stats = [&](float shift, float s1, float s2, float& mean, float& rstd, float (&off)[NG]) {
+        auto row_stats = [&](float shift, float s1, float s2, float& mean, float& rstd) {
             const float mg = shift + s1 / part_n;
             const float m2g = s2 - s1 * s1 / part_n;
             *red_mean = mg;
             *red_m2 = m2g;
-            *red_shift = shift;
             tc_fence_before();                  // the partner groups later read TMEM columns this warp stored
             named_bar_sync(pbar, 32 * NG);
             tc_fence_after();
@@ -362,14 +351,11 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 ms[i] = red[i * 128 + trow];
                 msum += ms[i];
                 m2 += red[NG * 128 + i * 128 + trow];
-                off[i] = red[2 * NG * 128 + i * 128 + trow];
             }
             mean = msum * (1.0f / NG);
 #pragma unroll
             for (int i = 0; i < NG; ++i) m2 = fmaf(part_n * (ms[i] - mean), ms[i] - mean, m2);
             rstd = rsqrtf(m2 * inv_c + p.ln_eps);
-#pragma unroll
-            for (int i = 0; i < NG; ++i) off[i] = (off[i] - mean) * rstd;
             named_bar_sync(pbar, 32 * NG);      // every partner has read the exchange slots before they are reused
         };
 
@@ -388,24 +374,6 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 0);
             float shift = 0.f, s1 = 0.f, s2 = 0.f;
             int waited = -1;
-            // The 16-bit fc1 operand (X1 - shift) of a chunk goes into Abuf one chunk late: Abuf still holds the O tile
-            // until the LAST proj N tile is complete, and by the second chunk that wait is (nearly) free.
-            uint32_t pk[16];
-            auto flush_operand = [&](int c_prev) {
-                if (waited != NB - 1) {
-                    waited = NB - 1;
-                    mbar_wait(&proj_bar[NB - 1], tc & 1);          // every proj MMA has read the O tile
-                    tc_fence_after();
-                }
-                uint8_t* kblk = abuf + static_cast<size_t>(c_prev >> 1) * G2_A_KB_BYTES;
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    *reinterpret_cast<uint4*>(kblk + slot_off(trow, 4 * (c_prev & 1) + j)) =
-                        make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-                fence_proxy_async_smem();          // generic writes -> visible to the tensor core's operand reads
-                __syncwarp();
-                if (lane == 0) mbar_arrive_leader(&ln2_bar[c_prev >> 1]);    // fc1 consumes the K block when both halves are in
-            };
 #ifdef DDC_PROBE_TIMING
             long long res_wait = 0;                // probes only: cycles this warp waited for residual chunks
 #endif
@@ -414,14 +382,13 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 const uint32_t s = static_cast<uint32_t>(k % SL);
                 uint8_t* slot = gslots + s * G2_GSLOT_BYTES;
                 const int n0 = c * 32;
-                if (n0 / BT_BN > waited) {
+                if (n0 / BT_BN != waited) {
                     waited = n0 / BT_BN;
                     mbar_wait(&proj_bar[waited], tc & 1);
                     tc_fence_after();
                 }
                 float v[32];
                 tmem_ld32(lane_taddr + n0, v);
-                if (k > 0) flush_operand(c - NG);
 #ifdef DDC_PROBE_TIMING
                 const long long w0 = (p.dbg != nullptr) ? clock64() : 0;
 #endif
@@ -439,12 +406,10 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 }
                 if (k == 0) shift = v[0];
 #pragma unroll
-                for (int i = 0; i < 32; i += 2) {
-                    const float d0 = v[i] - shift, d1 = v[i + 1] - shift;
-                    s1 += d0 + d1;
-                    s2 = fmaf(d0, d0, s2);
-                    s2 = fmaf(d1, d1, s2);
-                    pk[i >> 1] = pack2<F16>(d0, d1);
+                for (int i = 0; i < 32; ++i) {
+                    const float d = v[i] - shift;
+                    s1 += d;
+                    s2 = fmaf(d, d, s2);
                 }
                 tmem_st32(lane_taddr + n0, v);
                 if (k + SL < nper) {
@@ -456,19 +421,43 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     }
                 }
             }
-            flush_operand(hf + NG * (nper - 1));
             if (warp == 4 && lane == 0) {
                 bt_stamp(p, 1, tc * 16 + 1);
 #ifdef DDC_PROBE_TIMING
                 if (p.dbg != nullptr && blockIdx.x == 0 && tc < 4) p.dbg[128 + tc] = res_wait;
 #endif
             }
-            float mean, rstd, off[NG];
-            row_stats(shift, s1, s2, mean, rstd, off);
-            const float rstd2 = rstd;              // LayerNorm2's row scale and offsets, applied in epi2
-            float off2[NG];
+            float mean, rstd;
+            row_stats(shift, s1, s2, mean, rstd);
+            float nmr = -mean * rstd;              // (v - mean) * rstd * g + b  ==  fma(fma(v, rstd, nmr), g, b)
+            // LayerNorm2 -> Abuf (K-major, 128-byte swizzle: 64 columns = one K block).  All proj MMAs that read
+            // the O tile in Abuf completed before proj_bar[NB-1] fired.
+            for (int c = hf; c < C / 64; c += NG) {
+                uint8_t* kblk = abuf + static_cast<size_t>(c) * G2_A_KB_BYTES;
 #pragma unroll
-            for (int i = 0; i < NG; ++i) off2[i] = off[i];
+                for (int h = 0; h < 2; ++h) {
+                    float v[32];
+                    const int n0 = c * 64 + 32 * h;
+                    tmem_ld32(lane_taddr + n0, v);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float4 g0 = *reinterpret_cast<const float4*>(s_g2 + n0 + 8 * j);
+                        const float4 g1 = *reinterpret_cast<const float4*>(s_g2 + n0 + 8 * j + 4);
+                        const float4 b0 = *reinterpret_cast<const float4*>(s_b2 + n0 + 8 * j);
+                        const float4 b1 = *reinterpret_cast<const float4*>(s_b2 + n0 + 8 * j + 4);
+                        uint4 o;
+                        o.x = pack2<F16>(fmaf(fmaf(v[8 * j], rstd, nmr), g0.x, b0.x), fmaf(fmaf(v[8 * j + 1], rstd, nmr), g0.y, b0.y));
+                        o.y = pack2<F16>(fmaf(fmaf(v[8 * j + 2], rstd, nmr), g0.z, b0.z), fmaf(fmaf(v[8 * j + 3], rstd, nmr), g0.w, b0.w));
+                        o.z = pack2<F16>(fmaf(fmaf(v[8 * j + 4], rstd, nmr), g1.x, b1.x), fmaf(fmaf(v[8 * j + 5], rstd, nmr), g1.y, b1.y));
+                        o.w = pack2<F16>(fmaf(fmaf(v[8 * j + 6], rstd, nmr), g1.z, b1.z), fmaf(fmaf(v[8 * j + 7], rstd, nmr), g1.w, b1.w));
+                        *reinterpret_cast<uint4*>(kblk + slot_off(trow, 4 * h + j)) = o;
+                    }
+                }
+                fence_proxy_async_smem();          // generic writes -> visible to the tensor core's operand reads
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_leader(&ln2_bar[c]);    // fc1 can consume this K block right away
+            }
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 2);
 
             // ------------------------------------------------------------ epi2(j): H_j = gelu(acc + b_fc1) -> Hbuf
@@ -496,13 +485,9 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     const int jb = (c0 & 63) >> 3;                    // first 16-byte chunk inside the 128-byte row
 #pragma unroll
                     for (int i = 0; i < 32; i += 4) {
-                        const float4 b = *reinterpret_cast<const float4*>(s_beff + j * BT_BN + c0 + i);
-                        const float4 g0 = *reinterpret_cast<const float4*>(s_fg0 + j * BT_BN + c0 + i);
-                        const float4 g1 = *reinterpret_cast<const float4*>(s_fg1 + j * BT_BN + c0 + i);
-                        v[i] = gelu_erf(fmaf(v[i], rstd2, fmaf(off2[0], g0.x, fmaf(off2[1], g1.x, b.x))));
-                        v[i + 1] = gelu_erf(fmaf(v[i + 1], rstd2, fmaf(off2[0], g0.y, fmaf(off2[1], g1.y, b.y))));
-                        v[i + 2] = gelu_erf(fmaf(v[i + 2], rstd2, fmaf(off2[0], g0.z, fmaf(off2[1], g1.z, b.z))));
-                        v[i + 3] = gelu_erf(fmaf(v[i + 3], rstd2, fmaf(off2[0], g0.w, fmaf(off2[1], g1.w, b.w))));
+                        const float4 b = *reinterpret_cast<const float4*>(s_bfc1 + j * BT_BN + c0 + i);
+                        v[i] = gelu_erf(v[i] + b.x); v[i + 1] = gelu_erf(v[i + 1] + b.y);
+                        v[i + 2] = gelu_erf(v[i + 2] + b.z); v[i + 3] = gelu_erf(v[i + 3] + b.w);
                     }
 #pragma unroll
                     for (int jj = 0; jj < 4; ++jj) {
@@ -562,8 +547,8 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 }
             }
             if (warp == 4 && lane == 0) bt_stamp(p, 1, tc * 16 + 10);
-            row_stats(shift, s1, s2, mean, rstd, off);
-            const float nmr = -mean * rstd;        // (v - mean) * rstd * g + b  ==  fma(fma(v, rstd, nmr), g, b)
+            row_stats(shift, s1, s2, mean, rstd);
+            nmr = -mean * rstd;
             for (int c = hf; c < C / 64; c += NG, ++ri) {
                 uint8_t* slot = gslots + (ri % SL) * G2_GSLOT_BYTES;
                 if (gleader) bulk_wait_read<SL - 1>();   // the store that last used this slot has read it
@@ -611,41 +596,6 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     __syncthreads();
     cluster_sync_all();
     if (warp == 2) tmem_dealloc<2>(tmem_base, 512);
-}
-
-// Pack-time fold of LayerNorm2 into fc1 (see the head comment of this file): w1s = 16-bit(gamma o W1), g0 / g1 = row sums
-// of the ROUNDED w1s over the even / odd 32-column chunks, beff = beta * W1^T + b1.  One block per output row.  The source
-// weight is fp32 (ddc_pack_weights) or already 16 bit (the kernel-level entry point): SRC16.
-template <bool F16, bool SRC16>
-__global__ void __launch_bounds__(128) fold_ln_fc1_kernel(const void* __restrict__ w1, const float* __restrict__ gamma,
-                                                          const float* __restrict__ beta, const float* __restrict__ b1,
-                                                          bf16* __restrict__ w1s, float* __restrict__ g0, float* __restrict__ g1,
-                                                          float* __restrict__ beff, int C) {
-    const int o = blockIdx.x;
-    float a0 = 0.f, a1 = 0.f, ab = 0.f;
-    for (int k = threadIdx.x; k < C; k += blockDim.x) {
-        const size_t i = static_cast<size_t>(o) * C + k;
-        const float w = SRC16 ? unpack1<F16>(reinterpret_cast<const uint16_t*>(w1)[i]) : reinterpret_cast<const float*>(w1)[i];
-        const uint16_t r = static_cast<uint16_t>(pack2<F16>(gamma[k] * w, 0.f) & 0xFFFFu);
-        reinterpret_cast<uint16_t*>(w1s)[i] = r;
-        const float wr = unpack1<F16>(r);
-        if ((k >> 5) & 1) a1 += wr; else a0 += wr;
-        ab = fmaf(beta[k], w, ab);
-    }
-    __shared__ float red[3][4];
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        a0 += __shfl_xor_sync(0xffffffffu, a0, s);
-        a1 += __shfl_xor_sync(0xffffffffu, a1, s);
-        ab += __shfl_xor_sync(0xffffffffu, ab, s);
-    }
-    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = a0; red[1][threadIdx.x >> 5] = a1; red[2][threadIdx.x >> 5] = ab; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        g0[o] = (red[0][0] + red[0][1]) + (red[0][2] + red[0][3]);
-        g1[o] = (red[1][0] + red[1][1]) + (red[1][2] + red[1][3]);
-        beff[o] = (red[2][0] + red[2][1]) + (red[2][2] + red[2][3]) + b1[o];
-    }
 }
 
 }  // namespace ddc

@@ -394,9 +394,7 @@ struct LayerW {
     float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *b_qkv, *b_proj, *b_fc1, *b_fc2;
     bf16 *w_qkv, *w_proj, *w_fc1, *w_fc2;
     CUtensorMap tm_qkv[2], tm_proj[2], tm_fc1[2], tm_fc2[2];   // W tile boxes for cluster size 1 and 2
-    CUtensorMap tm_fc1_tail;                                  // gamma2-scaled fc1 as 64-row half tiles (fused block tail)
-    bf16* w_fc1s;                                             // 16-bit(gamma2 o Wfc1): LayerNorm2 folded into fc1 (block_tail.cuh)
-    float *fc1_g0, *fc1_g1, *fc1_beff;                        // its column-group sums and beta2 Wfc1^T + b_fc1
+    CUtensorMap tm_fc1_tail;                                  // fc1 as 64-row half tiles (fused block tail)
     bf16* w_qkv_hp;                                           // qkv weight rows regrouped per head pair (fused qkv + attention)
     float* b_qkv_hp;
     CUtensorMap tm_qkv_hp;                                    // box 64 x 96
@@ -508,7 +506,6 @@ static void carve(ddc_plan* pl, void* weight_arena, void* work_arena, size_t* wb
         l.w_fc1 = w.take<bf16>(C * C);  l.b_fc1 = w.take<float>(C);
         l.w_fc2 = w.take<bf16>(C * C);  l.b_fc2 = w.take<float>(C);
         l.w_qkv_hp = w.take<bf16>(3 * C * C);  l.b_qkv_hp = w.take<float>(3 * C);
-        l.w_fc1s = w.take<bf16>(C * C);  l.fc1_g0 = w.take<float>(C);  l.fc1_g1 = w.take<float>(C);  l.fc1_beff = w.take<float>(C);
     }
     pl->lnf_g = w.take<float>(C);
     pl->lnf_b = w.take<float>(C);
@@ -610,7 +607,7 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
             mk(&l.tm_fc2[cs - 1], false, l.w_fc2, C, C, pl->bn_row / cs);
         }
     }
-    for (auto& l : pl->layers) mk(&l.tm_fc1_tail, false, l.w_fc1s, C, C, 64);
+    for (auto& l : pl->layers) mk(&l.tm_fc1_tail, false, l.w_fc1, C, C, 64);
     if (r != DDC_OK) {
         delete pl;
         return r;
@@ -706,10 +703,6 @@ extern "C" int ddc_pack_weights(ddc_plan* pl, const float* const* t, int32_t n_t
         pack(b[4], l.w_proj, C, C, C);  copy(b[5], l.b_proj, C);
         copy(b[6], l.ln2_g, C);  copy(b[7], l.ln2_b, C);
         pack(b[8], l.w_fc1, C, C, C);  copy(b[9], l.b_fc1, C);
-        if (!pl->f32) {
-            if (pl->f16) fold_ln_fc1_kernel<true, false><<<C, 128, 0, st>>>(b[8], b[6], b[7], b[9], l.w_fc1s, l.fc1_g0, l.fc1_g1, l.fc1_beff, C);
-            else fold_ln_fc1_kernel<false, false><<<C, 128, 0, st>>>(b[8], b[6], b[7], b[9], l.w_fc1s, l.fc1_g0, l.fc1_g1, l.fc1_beff, C);
-        }
         pack(b[10], l.w_fc2, C, C, C);  copy(b[11], l.b_fc2, C);
     }
     const float* const* e = t + 5 + 12 * pl->sh.depth;
@@ -912,7 +905,7 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
         if (block_tail_usable(M, C, pl->bn_row)) {
             BlockTailParams bt{};
             bt.M = M; bt.C = C; bt.ln_eps = 1e-5f;
-            bt.b_proj = l.b_proj; bt.fc1_g0 = l.fc1_g0; bt.fc1_g1 = l.fc1_g1; bt.fc1_beff = l.fc1_beff; bt.b_fc2 = l.b_fc2;
+            bt.b_proj = l.b_proj; bt.ln2_g = l.ln2_g; bt.ln2_b = l.ln2_b; bt.b_fc1 = l.b_fc1; bt.b_fc2 = l.b_fc2;
             bt.lnn_g = lnn_g; bt.lnn_b = lnn_b;
             if (f16) TRY((launch_block_tail_inst<true>(pl->tm_O, l.tm_proj[1], l.tm_fc1_tail, l.tm_fc2[1], pl->tm_Xld, pl->st_X, pl->st_XN, bt, st)));
             else TRY((launch_block_tail_inst<false>(pl->tm_O, l.tm_proj[1], l.tm_fc1_tail, l.tm_fc2[1], pl->tm_Xld, pl->st_X, pl->st_XN, bt, st)));
@@ -1313,28 +1306,24 @@ extern "C" int ddc_k_embed(int32_t fmt, int32_t batch, int32_t L, int32_t C, int
 extern "C" int ddc_k_block_tail(int32_t fmt, int32_t M, int32_t C, const void* O, const void* Wproj, const float* b_proj,
                                 const float* ln2_g, const float* ln2_b, const void* Wfc1, const float* b_fc1,
                                 const void* Wfc2, const float* b_fc2, const float* lnn_g, const float* lnn_b, float* x,
-                                void* xn, void* w1s, float* vec3, void* stream) {
-    if (!O || !Wproj || !b_proj || !ln2_g || !ln2_b || !Wfc1 || !b_fc1 || !Wfc2 || !b_fc2 || !lnn_g || !lnn_b || !x || !xn || !w1s || !vec3)
+                                void* xn, void* stream) {
+    if (!O || !Wproj || !b_proj || !ln2_g || !ln2_b || !Wfc1 || !b_fc1 || !Wfc2 || !b_fc2 || !lnn_g || !lnn_b || !x || !xn)
         return fail(DDC_E_INVALID, "NULL tensor");
     if (M < 129 || C % 128 != 0 || C > 384 || C <= 0)
         return fail(DDC_E_INVALID, "block tail needs M > 128 and embed_dim in {128, 256, 384} (M=%d C=%d)", M, C);
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    // LayerNorm2 folded into fc1 (what ddc_pack_weights does once per model): scaled weight + three vectors in the scratch
-    if (fmt == 1) fold_ln_fc1_kernel<true, true><<<C, 128, 0, st>>>(Wfc1, ln2_g, ln2_b, b_fc1, static_cast<bf16*>(w1s), vec3, vec3 + C, vec3 + 2 * C, C);
-    else fold_ln_fc1_kernel<false, true><<<C, 128, 0, st>>>(Wfc1, ln2_g, ln2_b, b_fc1, static_cast<bf16*>(w1s), vec3, vec3 + C, vec3 + 2 * C, C);
-    CK(cudaGetLastError());
     const uint64_t Mp = (static_cast<uint64_t>(M) + G2_BM - 1) / G2_BM * G2_BM;
     CUtensorMap tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN;
     TRY(make_tmap(&tmO, false, O, Mp, C, G2_BM));
     TRY(make_tmap(&tmWp, false, Wproj, C, C, 64));
-    TRY(make_tmap(&tmW1, false, w1s, C, C, 64));
+    TRY(make_tmap(&tmW1, false, Wfc1, C, C, 64));
     TRY(make_tmap(&tmW2, false, Wfc2, C, C, 64));
     TRY(make_tmap(&tmXld, true, x, Mp, C, G2_BM));
     TRY(make_tmap(&tmXst, true, x, M, C, G2_BM));
     TRY(make_tmap(&tmXN, false, xn, M, C, G2_BM));
     BlockTailParams bt{};
     bt.M = M; bt.C = C; bt.ln_eps = 1e-5f;
-    bt.b_proj = b_proj; bt.fc1_g0 = vec3; bt.fc1_g1 = vec3 + C; bt.fc1_beff = vec3 + 2 * C; bt.b_fc2 = b_fc2; bt.lnn_g = lnn_g; bt.lnn_b = lnn_b;
+    bt.b_proj = b_proj; bt.ln2_g = ln2_g; bt.ln2_b = ln2_b; bt.b_fc1 = b_fc1; bt.b_fc2 = b_fc2; bt.lnn_g = lnn_g; bt.lnn_b = lnn_b;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (fmt == 1) return launch_block_tail_inst<true>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, bt, st);
     return launch_block_tail_inst<false>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, bt, st);
 }

@@ -59,7 +59,7 @@ def test_arena_bytes_and_shape_validation():
     wb, kb = C.c_size_t(), C.c_size_t()
     s1 = _lib.Shape(64, 64, 8, 384, 7, 12, 3, 2000)
     assert lib.ddc_arena_bytes(C.byref(s1), 1024, C.byref(wb), C.byref(kb)) == 0
-    assert 15e6 < wb.value < 26e6          # 12.8 MB 16-bit weights + 6.2 MB head-pair copy of qkv + 2.1 MB gamma-scaled fc1 + 3 MB fp32 time table + biases
+    assert 15e6 < wb.value < 25e6          # 12.8 MB 16-bit weights + 6.2 MB head-pair copy of the qkv weights + 3 MB fp32 time table + biases
     assert kb.value < 600e6
     bad = _lib.Shape(64, 64, 8, 192, 7, 3, 3, 2000)     # DINO vit_tiny: 192 is not a multiple of 64 ... head_dim 64
     assert lib.ddc_arena_bytes(C.byref(bad), 8, C.byref(wb), C.byref(kb)) == 0
