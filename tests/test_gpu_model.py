@@ -123,6 +123,12 @@ def test_batch_invariant_on_the_fused_path():
     c = m.sampler("cuda", 200, 1, noise=x[3:4])
     d = m.sampler("cuda", 200, 2, noise=x[3:5])
     assert torch.equal(a[3:4], c) and torch.equal(a[3:5], d)
+    # 296 images = 74 four-image tiles on 74 CTA pairs: the fused qkv + attention kernel then takes whole tiles as work units,
+    # where the small batches above cut every tile into two (per-launch cost model) -- a sample's bits must not depend on it
+    big = torch.from_numpy(O.synth_noise((296, 3, 32, 32), seed=10))
+    big[100:105] = x
+    e = m.sampler("cuda", 200, 296, noise=big)
+    assert torch.equal(e[100:105], a)
 
 
 def test_sequence_cold_d2d_tiny(tiny):
