@@ -317,3 +317,27 @@ def test_fp32_mode_s3_forward(golden):
     err = float(np.abs(y - g["fwd_y"]).max())
     print(f"s3 fp32 mode forward: max|y err| = {err:.3e}")
     assert err < EPS_TOL_FP32
+
+
+def test_s1_full_batch_properties_of_the_benchmarked_configuration():
+    """BASELINE config #2 at full size (S1, 1024 images): properties that need no oracle.  (1) Every image's prediction
+    equals the prediction of the same image in a batch of four (the fused qkv + attention kernel cuts the work
+    differently for the two batch sizes); (2) two runs are bit-identical; (3) the plan reports the fused path for this
+    shape in a 16-bit format and not in fp32 mode."""
+    from ddim_cold_b200 import _lib
+    from oracle import ddim_oracle as O
+    sh = O.S1
+    m = build(sh, O.synth_state_dict(sh, seed=0, rich=True))
+    x = torch.from_numpy(O.synth_noise((1024, 3, sh.img_h, sh.img_w), seed=77)).cuda()
+    t = (torch.arange(1024, device="cuda") * 37 + 11) % sh.total_steps
+    y = m(x, t)
+    assert torch.isfinite(y).all()
+    assert torch.equal(y, m(x, t))
+    for lo in (0, 508, 1020):
+        assert torch.equal(y[lo:lo + 4], m(x[lo:lo + 4], t[lo:lo + 4])), lo
+    lib = _lib.load()
+    plan = m._plan(torch.device("cuda", torch.cuda.current_device()), 4)
+    assert lib.ddc_plan_fused_qkv_attention(plan.handle) == 1
+    m.operand_format = "fp32"
+    plan = m._plan(torch.device("cuda", torch.cuda.current_device()), 4)
+    assert lib.ddc_plan_fused_qkv_attention(plan.handle) == 0
