@@ -51,6 +51,7 @@ SIGNATURES = {
     "ddc_launches_per_step": (C.c_int, [_vp]),
     "ddc_plan_max_batch": (C.c_int, [_vp]),
     "ddc_plan_fused_qkv_attention": (C.c_int, [_vp]),
+    "ddc_plan_set_fused_qkv_attention": (C.c_int, [_vp, _i32]),
     "ddc_profile_steps": (C.c_int, [_vp, _vp, _i32, C.POINTER(Step), _i32, C.POINTER(C.c_float), C.POINTER(_i32), _vp]),
     "ddc_plan_set_operand_format": (C.c_int, [_vp, _i32]),
     "ddc_k_gemm": (C.c_int, [_i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _vp]),

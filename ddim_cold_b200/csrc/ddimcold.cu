@@ -415,6 +415,7 @@ struct ddc_plan {
     int bn_qkv, bn_fc1, bn_row, bn_head;
     bool packed;
     bool f16;       // 16-bit operand format: false = bfloat16 (default), true = IEEE half
+    bool separate_qkv_attn;   // ddc_plan_set_fused_qkv_attention(plan, 0): qkv GEMM and attention as two kernels for every shape
     bool f32;       // fp32 mode: every contraction in fp32 on the CUDA cores (fp32_path.cuh); overrides f16
     // fp32 mode reads the weight matrices where the caller keeps them (state_dict tensors given to ddc_pack_weights)
     const float* w32_patch;
@@ -573,6 +574,7 @@ extern "C" int ddc_plan_create(const ddc_shape* shape, int32_t max_batch, int32_
     pl->packed = false;
     pl->f16 = false;
     pl->f32 = false;
+    pl->separate_qkv_attn = false;
     pl->gexec = nullptr;
     pl->gkey = GraphKey{0, nullptr, nullptr, nullptr, nullptr};
     pl->fixed_view_cap = 0;
@@ -662,7 +664,18 @@ extern "C" int ddc_launches_per_step(const ddc_plan* plan) {
 
 extern "C" int ddc_plan_fused_qkv_attention(const ddc_plan* plan) {
     if (plan == nullptr || plan->f32) return 0;
-    return qkv_attn_usable(plan->L, plan->C, plan->sh.heads) ? 1 : 0;
+    return (!plan->separate_qkv_attn && qkv_attn_usable(plan->L, plan->C, plan->sh.heads)) ? 1 : 0;
+}
+
+extern "C" int ddc_plan_set_fused_qkv_attention(ddc_plan* plan, int32_t enable) {
+    if (plan == nullptr) return fail(DDC_E_INVALID, "plan is NULL");
+    const bool sep = enable == 0;
+    if (plan->separate_qkv_attn != sep && plan->gexec) {      // the captured step graph holds the other kernel sequence
+        cudaGraphExecDestroy(plan->gexec);
+        plan->gexec = nullptr;
+    }
+    plan->separate_qkv_attn = sep;
+    return DDC_OK;
 }
 
 // ------------------------------------------------------------------------------- packing
@@ -881,7 +894,7 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
         LayerW& l = pl->layers[i];
         Gemm2Params q{};
         q.N = 3 * C; q.K = C; q.bn = pl->bn_qkv; q.bias = l.b_qkv;
-        if (qkv_attn_usable(L, C, s.heads)) {
+        if (!pl->separate_qkv_attn && qkv_attn_usable(L, C, s.heads)) {
             // q | k | v of the class rows (one per image: a [B x 3C] GEMM over XN rows L apart), then qkv + attention of
             // the patch rows in one kernel that reads those class rows from L2
             const int ccs = gemm_cluster_size(B);

@@ -116,6 +116,11 @@ class DiffusionVisionTransformer(nn.Module):
     #: "fp32": every contraction in fp32 on the CUDA cores -- the reference's own precision (eps within 1e-4), a few
     #: per cent of the 16-bit throughput.
     operand_format = "fp16"
+    #: S1-like shapes (65 tokens, heads of 32) run the qkv Linear and attention as ONE kernel.  False selects the two
+    #: separate kernels for every batch size: the better choice for calls of fewer than ~256 images (0.28 vs 0.32 ms per
+    #: denoise step at N = 1).  The paths round differently: keep one setting wherever samples must be bit-identical
+    #: (all ranks of a sharded run), which is why the library does not switch by batch size on its own.
+    fused_qkv_attention = True
     _FORMATS = {"bf16": 0, "fp16": 1, "fp32": 2}
 
     def __init__(self, img_size=[64, 64], patch_size=8, in_chans=3, embed_dim=256, depth=3,
@@ -189,6 +194,7 @@ class DiffusionVisionTransformer(nn.Module):
             self._plans[device] = plan
         params = self._ordered_params()
         _lib.check(_lib.load().ddc_plan_set_operand_format(plan.handle, fmt))
+        _lib.check(_lib.load().ddc_plan_set_fused_qkv_attention(plan.handle, 1 if self.fused_qkv_attention else 0))
         key = (self.operand_format,) + tuple((p.data_ptr(), p._version) for p in params)
         if plan.packed_key != key:
             keep = []

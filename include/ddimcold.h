@@ -100,6 +100,12 @@ int ddc_plan_max_batch(const ddc_plan* plan);
  * For reports: the per-class timings of ddc_profile_steps then mean {class-row qkv GEMM, fused qkv + attention}. */
 int ddc_plan_fused_qkv_attention(const ddc_plan* plan);
 
+/* enable = 0: run the qkv Linear and attention as two kernels for every shape (what shapes other than 65 tokens / heads of
+ * 32 do anyway).  The fused kernel (default, enable = 1) is the faster one from about 256 images per call up; below that
+ * it pays one more dependent launch per block (0.32 vs 0.28 ms per denoise step at one image).  The two paths round
+ * differently, so use ONE setting for all calls whose samples must be bit-identical (e.g. all ranks of a sharded run). */
+int ddc_plan_set_fused_qkv_attention(ddc_plan* plan, int32_t enable);
+
 /* Pack an fp32 state dict into the plan's weight arena (bf16 K-major GEMM operands, folded
  * cls/pos/conv-bias rows, fp32 time table).  `tensors` is a HOST array of `n_tensors` device
  * pointers in the reference's state_dict order: cls_token, pos_embed, patch_embed.proj.weight,

@@ -341,3 +341,22 @@ def test_s1_full_batch_properties_of_the_benchmarked_configuration():
     m.operand_format = "fp32"
     plan = m._plan(torch.device("cuda", torch.cuda.current_device()), 4)
     assert lib.ddc_plan_fused_qkv_attention(plan.handle) == 0
+
+
+def test_separate_qkv_attention_setting_agrees_with_the_fused_kernel():
+    """`fused_qkv_attention = False` (the low-latency choice for small batches) runs the qkv GEMM and the attention kernel
+    separately: same prediction within the 16-bit tolerance, and the step graph is rebuilt when the setting flips."""
+    from oracle import ddim_oracle as O
+    sh = O.Shape(32, 32, 4, 128, 2, 4)
+    sd = O.synth_state_dict(sh, seed=3, rich=True)
+    m = build(sh, sd)
+    x = torch.from_numpy(O.synth_noise((6, 3, 32, 32), seed=21))
+    a = m.sampler("cuda", 200, 6, noise=x)
+    m.fused_qkv_attention = False
+    b = m.sampler("cuda", 200, 6, noise=x)
+    m.fused_qkv_attention = True
+    c = m.sampler("cuda", 200, 6, noise=x)
+    assert torch.equal(a, c)
+    assert not torch.equal(a, b) and (a - b).abs().max().item() < 5e-3
+    ref = O.sampler(sd, sh, x.numpy(), 200, np.float32)
+    assert np.abs(b.numpy() - ref).max() < 2e-2
