@@ -659,7 +659,11 @@ extern "C" int ddc_launches_per_step(const ddc_plan* plan) {
         fa_split_rows(plan->L, &n_qt, &rows_main);
         if (rows_main < plan->L) att = 2;
     }
-    return 2 + ((fused ? 2 : 4) + att) * plan->sh.depth + 2;
+    // inside the sampling loop patchify runs once per loop, not per step, when head_ddim can emit the next patch matrix
+    HeadDdimParams q{};
+    q.ldy = plan->P; q.H = plan->sh.img_h; q.W = plan->sh.img_w; q.p = plan->sh.patch; q.L = plan->L; q.Kp = plan->Kp;
+    const int patchify = (env_int("DDC_STEP_PATCHIFY", 0) || head_ddim_rows(q, true) == 0) ? 1 : 0;
+    return patchify + 1 + ((fused ? 2 : 4) + att) * plan->sh.depth + 2;
 }
 
 extern "C" int ddc_plan_fused_qkv_attention(const ddc_plan* plan) {
@@ -872,16 +876,18 @@ static int enqueue_predictor_f32(ddc_plan* pl, const float* x, int B, const int*
 // attention, proj GEMM (+residual, emits LN2), fc1 GEMM (+GELU), fc2 GEMM (+residual, emits the
 // next LayerNorm)] -> head GEMM.  Leaves the head output in pl->Y.
 static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_img, bool use_step_ctr, cudaStream_t st,
-                             Prof* prof = nullptr) {
+                             Prof* prof = nullptr, bool skip_patchify = false) {
     if (pl->f32) return enqueue_predictor_f32(pl, x, B, t_img, use_step_ctr, st, prof);
     const ddc_shape& s = pl->sh;
     const int C = pl->C, L = pl->L, M = B * L;
     TRY(ensure_store_maps(pl, B));
     const bool f16 = pl->f16;
     const int cs = gemm_cluster_size(M);
-    CK(f16 ? launch_patchify<true>(x, pl->Ap, B, s.img_h, s.img_w, s.patch, L, pl->Kp, use_step_ctr ? pl->ctr : nullptr, st)
-           : launch_patchify<false>(x, pl->Ap, B, s.img_h, s.img_w, s.patch, L, pl->Kp, use_step_ctr ? pl->ctr : nullptr, st));
-    MARK(KC_PATCHIFY);
+    if (!skip_patchify) {      // inside the sampling loop the previous step's head_ddim has already written Ap (see enqueue_step)
+        CK(f16 ? launch_patchify<true>(x, pl->Ap, B, s.img_h, s.img_w, s.patch, L, pl->Kp, use_step_ctr ? pl->ctr : nullptr, st)
+               : launch_patchify<false>(x, pl->Ap, B, s.img_h, s.img_w, s.patch, L, pl->Kp, use_step_ctr ? pl->ctr : nullptr, st));
+        MARK(KC_PATCHIFY);
+    }
     const LayerW& l0 = pl->layers[0];
     Gemm2Params g{};
     g.M = M; g.N = C; g.K = pl->Kp; g.bn = pl->bn_row; g.stages = pick_stages2(g.K, g.N, g.bn / cs, true);
@@ -1092,16 +1098,44 @@ extern "C" int ddc_forward_fixed_scratch(ddc_plan* pl, const float* x, const int
     return rc;
 }
 
-static int enqueue_step(ddc_plan* pl, float* x, int B, float* x0_last, float* x0_seq, float* eps_seq, cudaStream_t st,
-                        Prof* prof = nullptr) {
-    TRY(enqueue_predictor(pl, x, B, nullptr, true, st, prof));
+static HeadDdimParams step_head_params(ddc_plan* pl, float* x, int B, float* x0_last, float* x0_seq, float* eps_seq) {
     HeadDdimParams q{};
     q.y = pl->Y; q.ldy = pl->P; q.x = x;
     q.H = pl->sh.img_h; q.W = pl->sh.img_w; q.p = pl->sh.patch; q.L = pl->L; q.B = B;
     q.tbl = pl->tbl; q.cur = pl->ctr;
     q.x0_last = x0_last; q.x0_seq = x0_seq; q.eps_seq = eps_seq;
+    q.Kp = pl->Kp; q.f16 = pl->f16 ? 1 : 0;
+    return q;
+}
+
+// In the sampling loop the unpatchify + DDIM pass of a step can also write the NEXT step's patch matrix (it holds the updated
+// pixels anyway), which takes patchify -- a 50 MB read and a launch -- out of every step but the first.  Needs the vector
+// head_ddim kernel with room for the patch rows, and a 16-bit operand format.
+static bool step_emits_patches(ddc_plan* pl, float* x, int B, float* x0_last, float* x0_seq, float* eps_seq) {
+    if (pl->f32 || env_int("DDC_STEP_PATCHIFY", 0)) return false;
+    HeadDdimParams q = step_head_params(pl, x, B, x0_last, x0_seq, eps_seq);
+    q.ap_next = pl->Ap;
+    return head_ddim_rows(q, true) > 0;
+}
+
+// One denoise step.  emit_patches: head_ddim writes the next step's patch matrix and moves the step counter on, and
+// patchify is skipped here (the caller ran it once before the first step).
+static int enqueue_step(ddc_plan* pl, float* x, int B, float* x0_last, float* x0_seq, float* eps_seq, cudaStream_t st,
+                        Prof* prof = nullptr, bool emit_patches = false) {
+    TRY(enqueue_predictor(pl, x, B, nullptr, true, st, prof, emit_patches));
+    HeadDdimParams q = step_head_params(pl, x, B, x0_last, x0_seq, eps_seq);
+    if (emit_patches) { q.ap_next = pl->Ap; q.ctr_adv = pl->ctr; }
     CK(launch_head_ddim<MODE_STEP>(q, st));
     MARK(KC_DDIM);
+    return DDC_OK;
+}
+
+// The loop's one patchify (step counter: {0, 1}) when the steps emit their successors' patch matrices
+static int enqueue_first_patchify(ddc_plan* pl, const float* x, int B, cudaStream_t st, Prof* prof = nullptr) {
+    const ddc_shape& s = pl->sh;
+    CK(pl->f16 ? launch_patchify<true>(x, pl->Ap, B, s.img_h, s.img_w, s.patch, pl->L, pl->Kp, pl->ctr, st)
+               : launch_patchify<false>(x, pl->Ap, B, s.img_h, s.img_w, s.patch, pl->L, pl->Kp, pl->ctr, st));
+    MARK(KC_PATCHIFY);
     return DDC_OK;
 }
 
@@ -1117,14 +1151,16 @@ extern "C" int ddc_profile_steps(ddc_plan* pl, float* x, int32_t batch, const dd
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     CK(cudaSetDevice(pl->device));
     CK(cudaMemcpyAsync(pl->tbl, host_table, sizeof(StepEntry) * n_steps, cudaMemcpyHostToDevice, st));
-    CK(cudaMemsetAsync(pl->ctr, 0, 2 * sizeof(int), st));
+    CK(cudaMemsetAsync(pl->ctr, 0, 3 * sizeof(int), st));
     for (int c = 0; c < KC_COUNT; ++c) { class_ms[c] = 0.f; class_launches[c] = 0; }
     Prof prof;
     prof.st = st;
     int rc = DDC_OK;
+    const bool emit = step_emits_patches(pl, x, batch, nullptr, nullptr, nullptr);
     for (int i = 0; i < n_steps && rc == DDC_OK; ++i) {
         rc = prof.begin();
-        if (rc == DDC_OK) rc = enqueue_step(pl, x, batch, nullptr, nullptr, nullptr, st, &prof);
+        if (rc == DDC_OK && emit && i == 0) rc = enqueue_first_patchify(pl, x, batch, st, &prof);
+        if (rc == DDC_OK) rc = enqueue_step(pl, x, batch, nullptr, nullptr, nullptr, st, &prof, emit);
         if (rc != DDC_OK) break;
         const cudaError_t e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) { rc = fail(DDC_E_CUDA, "profile: %s", cudaGetErrorString(e)); break; }
@@ -1153,9 +1189,11 @@ extern "C" int ddc_sample(ddc_plan* pl, float* x, int32_t batch, const ddc_step*
     CK(cudaSetDevice(pl->device));
     // pageable-source async copies are staged before returning, so host_table may be freed by the caller
     CK(cudaMemcpyAsync(pl->tbl, host_table, sizeof(StepEntry) * n_steps, cudaMemcpyHostToDevice, st));
-    CK(cudaMemsetAsync(pl->ctr, 0, 2 * sizeof(int), st));
+    CK(cudaMemsetAsync(pl->ctr, 0, 3 * sizeof(int), st));
+    const bool emit = step_emits_patches(pl, x, batch, x0_last, x0_seq, eps_seq);
     if (!use_graph) {
-        for (int i = 0; i < n_steps; ++i) TRY(enqueue_step(pl, x, batch, x0_last, x0_seq, eps_seq, st));
+        if (emit) TRY(enqueue_first_patchify(pl, x, batch, st));
+        for (int i = 0; i < n_steps; ++i) TRY(enqueue_step(pl, x, batch, x0_last, x0_seq, eps_seq, st, nullptr, emit));
         return DDC_OK;
     }
     if (st == nullptr) return fail(DDC_E_INVALID, "graph replay needs a non-default stream (capture is illegal on stream 0)");
@@ -1167,7 +1205,7 @@ extern "C" int ddc_sample(ddc_plan* pl, float* x, int32_t batch, const ddc_step*
         }
         cudaGraph_t graph = nullptr;
         CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        const int r = enqueue_step(pl, x, batch, x0_last, x0_seq, eps_seq, st);
+        const int r = enqueue_step(pl, x, batch, x0_last, x0_seq, eps_seq, st, nullptr, emit);
         const cudaError_t e = cudaStreamEndCapture(st, &graph);
         if (r != DDC_OK) {
             if (graph) cudaGraphDestroy(graph);
@@ -1182,6 +1220,7 @@ extern "C" int ddc_sample(ddc_plan* pl, float* x, int32_t batch, const ddc_step*
         }
         pl->gkey = key;
     }
+    if (emit) TRY(enqueue_first_patchify(pl, x, batch, st));      // the captured step has no patchify of its own
     for (int i = 0; i < n_steps; ++i) CK(cudaGraphLaunch(pl->gexec, st));
     return DDC_OK;
 }

@@ -73,6 +73,12 @@ struct HeadDdimParams {
     float* x0_seq;      // [steps,B,3,H,W] or null
     float* eps_seq;     // [steps,B,3,H,W] or null
     int B;
+    // MODE_STEP, vector kernel only: also emit the NEXT step's patch matrix (what patchify would make of the updated x:
+    // 16-bit [B*L, Kp], column c*p*p + p1*p + p2), so that the loop runs patchify only once, and advance the step counter
+    // the way the next step's patchify would have (ctr[0] = ctr[1]; ctr[1] += 1; ctr[2] is the block ticket).
+    bf16* ap_next;      // or null
+    int Kp, f16;
+    int* ctr_adv;       // or null
 };
 
 template <int MODE>
@@ -207,6 +213,15 @@ __global__ void __launch_bounds__(256) head_ddim_rows_kernel(const HeadDdimParam
     const int Wp = W / p;
     const int P = 3 * p * p, PS = P + 1;
     const float* yrow = q.y + (static_cast<size_t>(b) * q.L + 1 + static_cast<size_t>(ph0) * Wp) * q.ldy;
+    // the next step's patch-matrix rows of this block, behind the y tile (16-byte aligned)
+    uint8_t* apt = reinterpret_cast<uint8_t*>(ys) + ((static_cast<size_t>(R) * Wp * PS * sizeof(float) + 15) & ~static_cast<size_t>(15));
+    if (MODE == MODE_STEP && q.ap_next != nullptr) {
+        const int padw = (q.Kp - P) >> 1;                    // zero K padding, in 32-bit words per row
+        for (int i = threadIdx.x; i < R * Wp * padw; i += blockDim.x) {
+            const int rr = i / padw, j = i - rr * padw;
+            *reinterpret_cast<uint32_t*>(apt + (static_cast<size_t>(rr) * q.Kp + P) * 2 + 4 * j) = 0u;
+        }
+    }
     const uint32_t p4 = rg.p4.d;
     const uint32_t nld = static_cast<uint32_t>(R * Wp) * p4;
     for (uint32_t i = threadIdx.x; i < nld; i += blockDim.x) {
@@ -244,14 +259,42 @@ __global__ void __launch_bounds__(256) head_ddim_rows_kernel(const HeadDdimParam
             v.x = fminf(fmaxf(v.x, -1.f), 1.f); v.y = fminf(fmaxf(v.y, -1.f), 1.f);
             v.z = fminf(fmaxf(v.z, -1.f), 1.f); v.w = fminf(fmaxf(v.w, -1.f), 1.f);
             const float4 xt = *reinterpret_cast<const float4*>(q.x + gi);
-            *reinterpret_cast<float4*>(q.x + gi) =
-                make_float4(e.a * xt.x + e.b * v.x, e.a * xt.y + e.b * v.y, e.a * xt.z + e.b * v.z, e.a * xt.w + e.b * v.w);
+            const float4 xn = make_float4(e.a * xt.x + e.b * v.x, e.a * xt.y + e.b * v.y, e.a * xt.z + e.b * v.z, e.a * xt.w + e.b * v.w);
+            *reinterpret_cast<float4*>(q.x + gi) = xn;
             if (q.x0_seq) *reinterpret_cast<float4*>(q.x0_seq + seq_off + gi) = v;
             if (q.eps_seq)
                 *reinterpret_cast<float4*>(q.eps_seq + seq_off + gi) =
                     make_float4((xt.x - e.sqrt_at * v.x) * e.inv_sqrt_1mat, (xt.y - e.sqrt_at * v.y) * e.inv_sqrt_1mat,
                                 (xt.z - e.sqrt_at * v.z) * e.inv_sqrt_1mat, (xt.w - e.sqrt_at * v.w) * e.inv_sqrt_1mat);
             if ((e.flags & 1) && q.x0_last) *reinterpret_cast<float4*>(q.x0_last + gi) = v;
+            if (q.ap_next != nullptr) {          // the updated pixels, in the patch matrix's layout and operand format
+                uint2 o;
+                if (q.f16) { o.x = pack2<true>(xn.x, xn.y); o.y = pack2<true>(xn.z, xn.w); }
+                else { o.x = pack2<false>(xn.x, xn.y); o.y = pack2<false>(xn.z, xn.w); }
+                *reinterpret_cast<uint2*>(apt + (static_cast<size_t>(r * Wp + pw) * q.Kp + c * p * p + p1 * p + p2) * 2) = o;
+            }
+        }
+    }
+    if (MODE == MODE_STEP && q.ap_next != nullptr) {
+        __syncthreads();
+        uint4* dst = reinterpret_cast<uint4*>(q.ap_next + (static_cast<size_t>(b) * q.L + 1 + static_cast<size_t>(ph0) * Wp) * q.Kp);
+        const int nvec = R * Wp * q.Kp / 8;
+        for (int i = threadIdx.x; i < nvec; i += blockDim.x) dst[i] = reinterpret_cast<const uint4*>(apt)[i];
+    }
+    if (MODE == MODE_STEP && q.ctr_adv != nullptr) {
+        // every block read the step index at its start; the block that finishes LAST moves the counter on
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            const unsigned total = gridDim.x * gridDim.y;
+            if (atomicAdd(reinterpret_cast<unsigned*>(q.ctr_adv + 2), 1u) == total - 1) {
+                volatile int* cv = q.ctr_adv;
+                const int nxt = cv[1];
+                cv[0] = nxt;
+                cv[1] = nxt + 1;
+                cv[2] = 0;
+                __threadfence();
+            }
         }
     }
 }
@@ -282,17 +325,30 @@ inline cudaError_t launch_patchify(const float* x, bf16* ap, int B, int H, int W
     return launch_chain(patchify_kernel<F16>, dim3(Hp, B), dim3(256), 0, st, 1, x, ap, H, W, p, L, Kp, step_ctr);
 }
 
+// Patch rows per block of the vector head_ddim kernel (0 = the shape needs the scalar kernel).  With `with_ap` the block
+// also holds its rows of the next step's patch matrix.
+inline int head_ddim_rows(const HeadDdimParams& q, bool with_ap) {
+    const int Hp = q.H / q.p, Wp = q.W / q.p;
+    const size_t row_bytes = static_cast<size_t>(Wp) * (3 * q.p * q.p + 1) * sizeof(float) +
+                             (with_ap ? static_cast<size_t>(Wp) * q.Kp * 2 + 16 : 0);
+    auto al16 = [](const void* ptr) { return reinterpret_cast<uintptr_t>(ptr) % 16 == 0; };
+    const bool aligned = al16(q.y) && al16(q.x) && al16(q.x0_last) && al16(q.x0_seq) && al16(q.eps_seq) && al16(q.ap_next);
+    if (with_ap && (q.Kp % 8 != 0 || (3 * q.p * q.p) % 2 != 0)) return 0;
+    return (q.W % 4 == 0 && q.p % 4 == 0 && q.ldy % 4 == 0 && aligned) ? rows_per_block(Hp, row_bytes, EW_TILE_BUDGET) : 0;
+}
+
 template <int MODE>
 inline cudaError_t launch_head_ddim(const HeadDdimParams& q, cudaStream_t st) {
     const int Hp = q.H / q.p, Wp = q.W / q.p;
-    const size_t row_bytes = static_cast<size_t>(Wp) * (3 * q.p * q.p + 1) * sizeof(float);
-    auto al16 = [](const void* ptr) { return reinterpret_cast<uintptr_t>(ptr) % 16 == 0; };
-    const bool aligned = al16(q.y) && al16(q.x) && al16(q.x0_last) && al16(q.x0_seq) && al16(q.eps_seq);
-    const int R = (q.W % 4 == 0 && q.p % 4 == 0 && q.ldy % 4 == 0 && aligned) ? rows_per_block(Hp, row_bytes, EW_TILE_BUDGET) : 0;
-    if (R > 0)
-        return launch_chain(head_ddim_rows_kernel<MODE>, dim3(Hp / R, q.B), dim3(256), R * row_bytes, st, 1, q,
-                            make_rowgroup(R, q.W, q.p));
-    return launch_chain(head_ddim_kernel<MODE>, dim3(Hp, q.B), dim3(256), row_bytes, st, 1, q);
+    const size_t y_bytes = static_cast<size_t>(Wp) * (3 * q.p * q.p + 1) * sizeof(float);
+    const bool with_ap = MODE == MODE_STEP && q.ap_next != nullptr;
+    const int R = head_ddim_rows(q, with_ap);
+    if (R > 0) {
+        const size_t smem = ((R * y_bytes + 15) & ~static_cast<size_t>(15)) + (with_ap ? static_cast<size_t>(R) * Wp * q.Kp * 2 : 0);
+        return launch_chain(head_ddim_rows_kernel<MODE>, dim3(Hp / R, q.B), dim3(256), smem, st, 1, q, make_rowgroup(R, q.W, q.p));
+    }
+    if (with_ap) return cudaErrorInvalidValue;          // the caller checks head_ddim_rows() before asking for the patch matrix
+    return launch_chain(head_ddim_kernel<MODE>, dim3(Hp, q.B), dim3(256), y_bytes, st, 1, q);
 }
 
 // ---------------------------------------------------------------------------- weight packing (one-off)

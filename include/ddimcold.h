@@ -164,7 +164,8 @@ int ddc_sample(ddc_plan* plan, float* x, int32_t batch, const ddc_step* host_tab
 int ddc_profile_steps(ddc_plan* plan, float* x, int32_t batch, const ddc_step* host_table, int32_t n_steps,
                       float* class_ms, int32_t* class_launches, void* stream);
 
-/* Number of kernel launches one ddc_forward / one step of ddc_sample issues. */
+/* Number of kernel launches one step of ddc_sample issues (inside the loop patchify runs once per loop, not per step,
+ * whenever the unpatchify + DDIM pass can write the next step's patch matrix itself; ddc_forward issues one more). */
 int ddc_launches_per_step(const ddc_plan* plan);
 
 /* ---- kernel-level entry points (unit tests; hosts that schedule kernels themselves) ----
