@@ -4,7 +4,15 @@
 #include <cstdio>
 using namespace ddc;
 
-__global__ void __launch_bounds__(640, 1) probe(int warps_per_quarter, int with_mma, int iters, long long* out) {
+#define LD32REGS(NAME, SHAPE) \
+__device__ __forceinline__ void NAME(uint32_t taddr, float* v) { \
+    asm volatile("tcgen05.ld.sync.aligned." SHAPE ".b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n\ttcgen05.wait::ld.sync.aligned;" \
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]), "=f"(v[8]), "=f"(v[9]), "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]), "=f"(v[15]), "=f"(v[16]), "=f"(v[17]), "=f"(v[18]), "=f"(v[19]), "=f"(v[20]), "=f"(v[21]), "=f"(v[22]), "=f"(v[23]), "=f"(v[24]), "=f"(v[25]), "=f"(v[26]), "=f"(v[27]), "=f"(v[28]), "=f"(v[29]), "=f"(v[30]), "=f"(v[31]) : "r"(taddr) : "memory"); }
+LD32REGS(ld_16x256b_x8, "16x256b.x8")
+LD32REGS(ld_16x128b_x16, "16x128b.x16")
+LD32REGS(ld_16x64b_x32, "16x64b.x32")
+
+__global__ void __launch_bounds__(640, 1) probe(int warps_per_quarter, int with_mma, int iters, long long* out, int shape) {
     extern __shared__ uint8_t raw[];
     __shared__ uint32_t slot;
     __shared__ uint64_t bar;
@@ -42,8 +50,12 @@ __global__ void __launch_bounds__(640, 1) probe(int warps_per_quarter, int with_
         named_bar_sync(1, 128 * warps_per_quarter);
         const long long t0 = clock64();
         for (int it = 0; it < iters; ++it) {
-            tmem_ld32(t + 32 * (it & 7), v);                  // columns [0, 256)
-            acc += v[it & 31];
+            const uint32_t a = t + 32 * (it & 7);             // columns [0, 256)
+            if (shape == 0) tmem_ld32(a, v);
+            else if (shape == 1) ld_16x256b_x8(a + ((it & 8) ? (16u << 16) : 0u), v);      // 16 lanes x 64 columns
+            else if (shape == 2) ld_16x128b_x16(a + ((it & 8) ? (16u << 16) : 0u), v);
+            else ld_16x64b_x32(a + ((it & 8) ? (16u << 16) : 0u), v);
+            acc += v[0] + v[17] + v[31];
         }
         const long long t1 = clock64();
         named_bar_sync(1, 128 * warps_per_quarter);
@@ -58,13 +70,14 @@ int main() {
     long long* d; cudaMalloc(&d, 32);
     cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
     const int iters = 2000;
-    for (int mma : {0, 1}) for (int w : {1, 2, 4}) {
+    for (int shape : {0, 1, 2, 3}) for (int mma : {0, 1}) for (int w : {1, 2, 4}) {
+        if (shape > 0 && (mma || w != 1)) continue;
         cudaMemset(d, 0, 32);
-        probe<<<1, 640, 66 * 1024>>>(w, mma, iters, d);
+        probe<<<1, 640, 66 * 1024>>>(w, mma, iters, d, shape);
         cudaError_t e = cudaDeviceSynchronize();
         long long h[4] = {0, 0, 0, 0}; cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost);
         const double bytes = 4096.0 * 4 * w * iters;          // 4 quarters x w warps x 4 KB per load
-        printf("warps/quarter=%d mma=%d: %s  %.0f cycles per load per warp, %.1f B/clk per SM", w, mma, cudaGetErrorString(e),
+        printf("shape=%d (0: 32x32b.x32, 1: 16x256b.x8, 2: 16x128b.x16, 3: 16x64b.x32) warps/quarter=%d mma=%d: %s  %.0f cycles per load per warp, %.1f B/clk per SM", shape, w, mma, cudaGetErrorString(e),
                double(h[0]) / iters, bytes / double(h[0]));
         if (mma) printf(", %.1f cycles per MMA (N = 256; 128 alone)", double(h[0]) / double(h[2] > 0 ? h[2] : 1));
         printf("\n");
