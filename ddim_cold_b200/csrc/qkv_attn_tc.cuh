@@ -41,7 +41,7 @@ constexpr uint32_t QT_S = 192, QT_SW = 144;
 
 inline size_t qkv_attn_tc_smem_bytes(int C, int stages) {
     return 1024 + static_cast<size_t>(C / 64) * G2_A_KB_BYTES + static_cast<size_t>(stages) * 96 * 128 + 3 * QT_TILE + QT_KTILE +
-           static_cast<size_t>(C / 64) * QA_NB * 4 + 1024 + 1536 + 1024;
+           static_cast<size_t>(C / 64) * QA_NB * 4 + 1024 + 1536 + 1024 + 8192;
 }
 
 __device__ __forceinline__ void tmem_ld1_nowait(uint32_t taddr, float& v) {
@@ -99,6 +99,7 @@ qkv_attn_tc_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C]
     uint64_t* o_full = bars + 41;         // [2] O of head h complete (commit)
     uint64_t* o_free = bars + 43;         // [2] O of head h read out: its columns may take the next S (4 softmax warps)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 46);
+    uint8_t* out_stage = reinterpret_cast<uint8_t*>(bars + 128);      // [8 softmax warps][16 rows x 64 B]: output rows on their way to global memory
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t crank = cluster_ctarank();
@@ -152,15 +153,18 @@ qkv_attn_tc_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C]
         const float* bias = smem_bias + hg * QA_NB;
 #pragma unroll 1
         for (int c = c0; c < c0 + 3; ++c) {
+            // the chunk's bias first: the TMEM read below is an asm statement with a memory clobber, nothing is scheduled
+            // across it, and shared-memory loads issued after it would add their latency to every chunk
+            float4 bb[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bb[j] = *reinterpret_cast<const float4*>(bias + 32 * c + 4 * j);
             float v[32];
             tmem_ld32(lane_taddr + 32 * c, v);
             uint8_t* row = (c < 2 ? smem_q : (c < 4 ? smem_k : smem_v)) + r * 128;
-            const float* b = bias + 32 * c;
             const int half = (c & 1) * 4;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const float4 b0 = *reinterpret_cast<const float4*>(b + 8 * j);
-                const float4 b1 = *reinterpret_cast<const float4*>(b + 8 * j + 4);
+                const float4 b0 = bb[2 * j], b1 = bb[2 * j + 1];
                 uint4 w;
                 w.x = pack2<F16>(v[8 * j] + b0.x, v[8 * j + 1] + b0.y);
                 w.y = pack2<F16>(v[8 * j + 2] + b0.z, v[8 * j + 3] + b0.w);
@@ -170,6 +174,8 @@ qkv_attn_tc_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C]
             }
             if constexpr (TRACE) { if (q == 0) qa_stamp(p, c0 == 0 ? 1 : 4, trace_it, 3 + c - c0); }
         }
+    };
+    auto drain_finish = [&]() {
         fence_proxy_async_smem();                                   // the tiles (and the class keys) are MMA operands
         tc_fence_before();
         named_bar_sync(1, 256);                                     // all eight draining warps of this CTA are done
@@ -273,6 +279,7 @@ qkv_attn_tc_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C]
                 if (it > 0) mbar_wait_parked(qkv_free, (it - 1) & 1u);
                 if constexpr (TRACE) { if (q == 0) qa_stamp(p, 1, it, 1); }
                 drain3(0, hg, it);
+                drain_finish();
                 if (q == 0) {
                     issue_s(it);
                     if constexpr (TRACE) { qa_stamp(p, 3, it, 1); }
@@ -366,24 +373,47 @@ qkv_attn_tc_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C]
                 mbar_wait_parked(&o_full[h], par);
                 tc_fence_after();
                 if constexpr (TRACE) { if (st0) qa_stamp(p, 2, it, 2); }
+                const float* vc = vcls + par * 128 + j * 64 + h * 32;
+                float4 vv[8];                                               // before the TMEM read (memory clobber), see the drain
+#pragma unroll
+                for (int c = 0; c < 8; ++c) vv[c] = *reinterpret_cast<const float4*>(vc + 4 * c);
                 float o[32];
                 tmem_ld32(row_taddr + 32 * j, o);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&o_free[h]);
-                const float* vc = vcls + par * 128 + j * 64 + h * 32;
-                if (img < p.B) {
-                    bf16* ob = p.out + (static_cast<size_t>(img) * QA_L + 1 + (r & 63)) * p.C + hg * 64 + h * 32;
+                uint4 w[4];
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const float4 v0 = *reinterpret_cast<const float4*>(vc + 8 * c), v1 = *reinterpret_cast<const float4*>(vc + 8 * c + 4);
-                        uint4 w;
-                        w.x = pack2<F16>(fmaf(pc, v0.x, o[8 * c]) * inv, fmaf(pc, v0.y, o[8 * c + 1]) * inv);
-                        w.y = pack2<F16>(fmaf(pc, v0.z, o[8 * c + 2]) * inv, fmaf(pc, v0.w, o[8 * c + 3]) * inv);
-                        w.z = pack2<F16>(fmaf(pc, v1.x, o[8 * c + 4]) * inv, fmaf(pc, v1.y, o[8 * c + 5]) * inv);
-                        w.w = pack2<F16>(fmaf(pc, v1.z, o[8 * c + 6]) * inv, fmaf(pc, v1.w, o[8 * c + 7]) * inv);
-                        *reinterpret_cast<uint4*>(ob + 8 * c) = w;
+                for (int c = 0; c < 4; ++c) {
+                    const float4 v0 = vv[2 * c], v1 = vv[2 * c + 1];
+                    w[c].x = pack2<F16>(fmaf(pc, v0.x, o[8 * c]) * inv, fmaf(pc, v0.y, o[8 * c + 1]) * inv);
+                    w[c].y = pack2<F16>(fmaf(pc, v0.z, o[8 * c + 2]) * inv, fmaf(pc, v0.w, o[8 * c + 3]) * inv);
+                    w[c].z = pack2<F16>(fmaf(pc, v1.x, o[8 * c + 4]) * inv, fmaf(pc, v1.y, o[8 * c + 5]) * inv);
+                    w[c].w = pack2<F16>(fmaf(pc, v1.z, o[8 * c + 6]) * inv, fmaf(pc, v1.w, o[8 * c + 7]) * inv);
+                }
+                // A thread owns a row (64 B of this head).  Stored straight from here, one instruction would touch 32 rows
+                // 16 B at a time -- half sectors at a 768-byte stride -- and the SM's load/store path stays clogged for ~2k
+                // cycles, stalling the drain warps' shared-memory traffic with it (measured).  Through 1 KB of staging per
+                // warp, an instruction writes eight rows' full 64-byte segments instead.
+                uint8_t* stg = out_stage + (warp - 8) * 1024;
+                bf16* ob = p.out + (static_cast<size_t>(img) * QA_L + 1 + ((q * 32) & 63)) * p.C + hg * 64 + h * 32;
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    if ((lane >> 4) == half) {
+                        const int rr = lane & 15;
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(stg + rr * 64 + ((c ^ ((rr >> 1) & 3)) << 4)) = w[c];
                     }
+                    __syncwarp();
+                    if (img < p.B) {
+#pragma unroll
+                        for (int k = 0; k < 2; ++k) {
+                            const int rr = (lane >> 2) + 8 * k, c = lane & 3;
+                            const uint4 val = *reinterpret_cast<const uint4*>(stg + rr * 64 + ((c ^ ((rr >> 1) & 3)) << 4));
+                            *reinterpret_cast<uint4*>(ob + static_cast<size_t>(16 * half + rr) * p.C + c * 8) = val;
+                        }
+                    }
+                    __syncwarp();
                 }
                 if constexpr (TRACE) { if (st0) qa_stamp(p, 2, it, 3); }
             }
@@ -415,16 +445,15 @@ qkv_attn_tc_kernel(const __grid_constant__ CUtensorMap tmA,      // XN [B*65, C]
                 }
                 if (it > 0) mbar_wait_parked(qkv_free, (it - 1) & 1u);             // also: the output pass of it - 2 has read this parity
                 if constexpr (TRACE) { if (cw == 0) qa_stamp(p, 4, it, 0); }
+                mbar_wait_parked(tfull_bar, par);                           // second half of the accumulator drain first: it is
+                tc_fence_after();                                           // what the next S and the next GEMM wait for
+                drain3(3, hg, it);
                 // class key -> row 128 + j of the K tile (swizzle term (128 + j) & 7 = j), so S gets a class-score column
                 if (lane < 4) *reinterpret_cast<uint4*>(smem_k + (128 + j) * 128 + (((h * 4 + lane) ^ j) << 4)) = kraw;
                 vcls[par * 128 + j * 64 + h * 32 + lane] = vf;
                 qs[lane] = qf;
-                fence_proxy_async_smem();
-                __syncwarp();
+                drain_finish();                                             // (its fence covers the class key too)
                 if (lane == 0) mbar_arrive(cls_ready);
-                mbar_wait_parked(tfull_bar, par);                           // second half of the accumulator drain
-                tc_fence_after();
-                drain3(3, hg, it);
                 float scl = qf * kf;                                        // class query x class key
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) scl += __shfl_xor_sync(0xffffffffu, scl, o);
