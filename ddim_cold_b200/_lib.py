@@ -57,7 +57,7 @@ SIGNATURES = {
     "ddc_k_gemm": (C.c_int, [_i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
     "ddc_k_gemm_resid_ln": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ddc_k_embed": (C.c_int, [_i32] * 6 + [_vp] * 10),
-    "ddc_k_block_tail": (C.c_int, [_i32, _i32, _i32] + [_vp] * 14),
+    "ddc_k_block_tail": (C.c_int, [_i32, _i32, _i32] + [_vp] * 10),
     "ddc_k_attention": (C.c_int, [_i32, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "ddc_k_qkv_attn": (C.c_int, [_i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "ddc_k_patchify": (C.c_int, [_i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),

@@ -2,6 +2,8 @@
 //
 //     X1 = X + O * Wproj^T + b_proj                       (attention projection + residual)
 //     H  = gelu_erf(LayerNorm2(X1) * Wfc1^T + b_fc1)
+//          (the affine part of every LayerNorm is folded into the weight and bias of the Linear that consumes it at pack
+//           time -- W' = W o gamma, b' = b + W beta -- so the kernels only normalise: no per-column vectors to load)
 //     X' = X1 + H * Wfc2^T + b_fc2                        (MLP + residual)        -> X  (fp32)
 //     XN = LayerNorm_next(X')                                                      -> XN (16 bit)
 //
@@ -40,12 +42,8 @@ struct BlockTailParams {
     int M, C, stages, num_tiles;
     int gk;                  // K blocks (of 64) per W ring stage: 1 or 2.  One handshake moves gk * 8 KB per CTA.
     const float* b_proj;
-    const float* ln2_g;
-    const float* ln2_b;
-    const float* b_fc1;
+    const float* b_fc1;      // with LayerNorm2's beta folded in (and Wfc1 carries its gamma)
     const float* b_fc2;
-    const float* lnn_g;      // LayerNorm that follows the block (next block's norm1, or the final norm)
-    const float* lnn_b;
     float ln_eps;
     long long* dbg;          // probes only: [role 2][64] SM clock stamps of CTA 0, [128..] wait accounting
     int flags;               // tuning: bit 0 = L2-prefetch the next tile's O / residual rows (measured: no gain);
@@ -63,7 +61,7 @@ __device__ __forceinline__ void bt_stamp(const BlockTailParams& p, int role, int
 
 inline size_t block_tail_smem_bytes(int C, int stages, int gk) {
     return 1024 + static_cast<size_t>(C / 64) * G2_A_KB_BYTES + 2 * BT_HSLOT_BYTES + static_cast<size_t>(stages) * gk * 64 * 128 +
-           ((static_cast<size_t>(7) * C * 4 + 127) & ~static_cast<size_t>(127)) + BT_TAIL_BYTES;
+           ((static_cast<size_t>(3) * C * 4 + 127) & ~static_cast<size_t>(127)) + BT_TAIL_BYTES;
 }
 
 template <bool F16, int NG>
@@ -92,7 +90,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     uint8_t* ring = hbuf + 2 * BT_HSLOT_BYTES;
     float* sp = reinterpret_cast<float*>(ring + static_cast<size_t>(p.stages) * kStageBytes);
     uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sp) +
-                                                 ((static_cast<size_t>(7) * C * 4 + 127) & ~static_cast<size_t>(127)));
+                                                 ((static_cast<size_t>(3) * C * 4 + 127) & ~static_cast<size_t>(127)));
     uint64_t* full_bar = bars;            // [8]  W ring: TMA -> MMA            (leader's copy collects both CTAs' bytes)
     uint64_t* empty_bar = bars + 8;       // [8]  W ring: MMA -> TMA            (pair commit)
     uint64_t* afull_bar = bars + 16;      // [8]  O K block landed              (leader)
@@ -143,8 +141,8 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         tmem_relinquish<2>();
     }
     if (warp >= 4) {
-        const float* src[7] = {p.b_proj, p.ln2_g, p.ln2_b, p.b_fc1, p.b_fc2, p.lnn_g, p.lnn_b};
-        for (int i = threadIdx.x - 128; i < 7 * C; i += 128 * NG) sp[i] = src[i / C][i % C];
+        const float* src[3] = {p.b_proj, p.b_fc1, p.b_fc2};
+        for (int i = threadIdx.x - 128; i < 3 * C; i += 128 * NG) sp[i] = src[i / C][i % C];
     }
     tc_fence_before();
     __syncthreads();
@@ -170,12 +168,8 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
         else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
     }
     const float* s_bproj = sp;
-    const float* s_g2 = sp + C;
-    const float* s_b2 = sp + 2 * C;
-    const float* s_bfc1 = sp + 3 * C;
-    const float* s_bfc2 = sp + 4 * C;
-    const float* s_gn = sp + 5 * C;
-    const float* s_bn = sp + 6 * C;
+    const float* s_bfc1 = sp + C;
+    const float* s_bfc2 = sp + 2 * C;
 
     if (warp == 0 || warp == 3) {
         // ================================================================= TMA producers (alternate loads)
@@ -429,7 +423,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             }
             float mean, rstd;
             row_stats(shift, s1, s2, mean, rstd);
-            float nmr = -mean * rstd;              // (v - mean) * rstd * g + b  ==  fma(fma(v, rstd, nmr), g, b)
+            float nmr = -mean * rstd;              // (v - mean) * rstd  ==  fma(v, rstd, nmr)
             // LayerNorm2 -> Abuf (K-major, 128-byte swizzle: 64 columns = one K block).  All proj MMAs that read
             // the O tile in Abuf completed before proj_bar[NB-1] fired.
             for (int c = hf; c < C / 64; c += NG) {
@@ -441,15 +435,11 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     tmem_ld32(lane_taddr + n0, v);
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        const float4 g0 = *reinterpret_cast<const float4*>(s_g2 + n0 + 8 * j);
-                        const float4 g1 = *reinterpret_cast<const float4*>(s_g2 + n0 + 8 * j + 4);
-                        const float4 b0 = *reinterpret_cast<const float4*>(s_b2 + n0 + 8 * j);
-                        const float4 b1 = *reinterpret_cast<const float4*>(s_b2 + n0 + 8 * j + 4);
                         uint4 o;
-                        o.x = pack2<F16>(fmaf(fmaf(v[8 * j], rstd, nmr), g0.x, b0.x), fmaf(fmaf(v[8 * j + 1], rstd, nmr), g0.y, b0.y));
-                        o.y = pack2<F16>(fmaf(fmaf(v[8 * j + 2], rstd, nmr), g0.z, b0.z), fmaf(fmaf(v[8 * j + 3], rstd, nmr), g0.w, b0.w));
-                        o.z = pack2<F16>(fmaf(fmaf(v[8 * j + 4], rstd, nmr), g1.x, b1.x), fmaf(fmaf(v[8 * j + 5], rstd, nmr), g1.y, b1.y));
-                        o.w = pack2<F16>(fmaf(fmaf(v[8 * j + 6], rstd, nmr), g1.z, b1.z), fmaf(fmaf(v[8 * j + 7], rstd, nmr), g1.w, b1.w));
+                        o.x = pack2<F16>(fmaf(v[8 * j], rstd, nmr), fmaf(v[8 * j + 1], rstd, nmr));
+                        o.y = pack2<F16>(fmaf(v[8 * j + 2], rstd, nmr), fmaf(v[8 * j + 3], rstd, nmr));
+                        o.z = pack2<F16>(fmaf(v[8 * j + 4], rstd, nmr), fmaf(v[8 * j + 5], rstd, nmr));
+                        o.w = pack2<F16>(fmaf(v[8 * j + 6], rstd, nmr), fmaf(v[8 * j + 7], rstd, nmr));
                         *reinterpret_cast<uint4*>(kblk + slot_off(trow, 4 * h + j)) = o;
                     }
                 }
@@ -562,15 +552,11 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                     for (int j = 0; j < 4; ++j) {
                         const float4 a0 = *reinterpret_cast<const float4*>(s_bfc2 + n0 + 8 * j);
                         const float4 a1 = *reinterpret_cast<const float4*>(s_bfc2 + n0 + 8 * j + 4);
-                        const float4 g0 = *reinterpret_cast<const float4*>(s_gn + n0 + 8 * j);
-                        const float4 g1 = *reinterpret_cast<const float4*>(s_gn + n0 + 8 * j + 4);
-                        const float4 b0 = *reinterpret_cast<const float4*>(s_bn + n0 + 8 * j);
-                        const float4 b1 = *reinterpret_cast<const float4*>(s_bn + n0 + 8 * j + 4);
                         uint4 o;
-                        o.x = pack2<F16>(fmaf(fmaf(v[8 * j] + a0.x, rstd, nmr), g0.x, b0.x), fmaf(fmaf(v[8 * j + 1] + a0.y, rstd, nmr), g0.y, b0.y));
-                        o.y = pack2<F16>(fmaf(fmaf(v[8 * j + 2] + a0.z, rstd, nmr), g0.z, b0.z), fmaf(fmaf(v[8 * j + 3] + a0.w, rstd, nmr), g0.w, b0.w));
-                        o.z = pack2<F16>(fmaf(fmaf(v[8 * j + 4] + a1.x, rstd, nmr), g1.x, b1.x), fmaf(fmaf(v[8 * j + 5] + a1.y, rstd, nmr), g1.y, b1.y));
-                        o.w = pack2<F16>(fmaf(fmaf(v[8 * j + 6] + a1.z, rstd, nmr), g1.z, b1.z), fmaf(fmaf(v[8 * j + 7] + a1.w, rstd, nmr), g1.w, b1.w));
+                        o.x = pack2<F16>(fmaf(v[8 * j] + a0.x, rstd, nmr), fmaf(v[8 * j + 1] + a0.y, rstd, nmr));
+                        o.y = pack2<F16>(fmaf(v[8 * j + 2] + a0.z, rstd, nmr), fmaf(v[8 * j + 3] + a0.w, rstd, nmr));
+                        o.z = pack2<F16>(fmaf(v[8 * j + 4] + a1.x, rstd, nmr), fmaf(v[8 * j + 5] + a1.y, rstd, nmr));
+                        o.w = pack2<F16>(fmaf(v[8 * j + 6] + a1.z, rstd, nmr), fmaf(v[8 * j + 7] + a1.w, rstd, nmr));
                         *reinterpret_cast<uint4*>(slot + slot_off(trow, 4 * h + j)) = o;
                     }
                 }
@@ -596,6 +582,33 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
     __syncthreads();
     cluster_sync_all();
     if (warp == 2) tmem_dealloc<2>(tmem_base, 512);
+}
+
+// Pack-time fold of a LayerNorm's affine part into the Linear that consumes it:  (n * gamma + beta) W^T + b  =
+// n (W o gamma)^T + (b + W beta), n the plainly normalised activations.  w_out = 16-bit(gamma o W) [N][k_pad], zero padded;
+// b_out = b + W beta (fp32, from the unrounded W).  One block per output row.
+template <bool F16>
+__global__ void __launch_bounds__(128) fold_ln_linear_kernel(const float* __restrict__ w, const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, const float* __restrict__ b,
+                                                             bf16* __restrict__ w_out, float* __restrict__ b_out, int K, int k_pad) {
+    const int o = blockIdx.x;
+    float acc = 0.f;
+    for (int k = threadIdx.x; k < k_pad; k += blockDim.x) {
+        const float wv = k < K ? w[static_cast<size_t>(o) * K + k] : 0.f;
+        const float gv = k < K ? gamma[k] : 0.f;
+        reinterpret_cast<uint16_t*>(w_out)[static_cast<size_t>(o) * k_pad + k] = static_cast<uint16_t>(pack2<F16>(gv * wv, 0.f) & 0xFFFFu);
+        if (k < K) acc = fmaf(beta[k], wv, acc);
+    }
+    __shared__ float red[4];
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) b_out[o] = b[o] + ((red[0] + red[1]) + (red[2] + red[3]));
+}
+
+__global__ void fill_f32_kernel(float* __restrict__ dst, float v, size_t n) {
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * blockDim.x) dst[i] = v;
 }
 
 }  // namespace ddc

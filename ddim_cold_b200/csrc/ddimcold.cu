@@ -711,20 +711,36 @@ extern "C" int ddc_pack_weights(ddc_plan* pl, const float* const* t, int32_t n_t
     pack(t[2], pl->w_patch, C, P, pl->Kp);
     pack_posb_kernel<<<148, 256, 0, st>>>(pos, cls, t[3], pl->posb, L, C, L + 127);
     copy(t[4], pl->time_tab, static_cast<size_t>(pl->sh.total_steps) * C);
+    // 16-bit formats: the affine part of every LayerNorm goes into the Linear that consumes it (W' = W o gamma,
+    // b' = b + W beta; norm1 -> qkv, norm2 -> fc1, final norm -> head), and the LayerNorm vectors in the arena become
+    // ones / zeros: the kernels that fuse a LayerNorm into their epilogue then only normalise (the fused block tail does not
+    // even load the vectors).  fp32 mode keeps the reference's form (its kernels read the caller's fp32 matrices).
+    auto fold = [&](const float* w, const float* g, const float* be, const float* bias, bf16* wout, float* bout, int n, int k, int kpad) {
+        if (pl->f16) fold_ln_linear_kernel<true><<<n, 128, 0, st>>>(w, g, be, bias, wout, bout, k, kpad);
+        else fold_ln_linear_kernel<false><<<n, 128, 0, st>>>(w, g, be, bias, wout, bout, k, kpad);
+    };
+    auto ln_vectors = [&](const float* g, const float* be, float* g_dst, float* b_dst) {
+        if (pl->f32) { copy(g, g_dst, C); copy(be, b_dst, C); return; }
+        fill_f32_kernel<<<4, 256, 0, st>>>(g_dst, 1.f, C);
+        fill_f32_kernel<<<4, 256, 0, st>>>(b_dst, 0.f, C);
+    };
     for (int i = 0; i < pl->sh.depth; ++i) {
         const float* const* b = t + 5 + 12 * i;
         LayerW& l = pl->layers[i];
-        copy(b[0], l.ln1_g, C);  copy(b[1], l.ln1_b, C);
-        pack(b[2], l.w_qkv, 3 * C, C, C);  copy(b[3], l.b_qkv, 3 * C);
+        ln_vectors(b[0], b[1], l.ln1_g, l.ln1_b);
+        if (pl->f32) copy(b[3], l.b_qkv, 3 * C);
+        else fold(b[2], b[0], b[1], b[3], l.w_qkv, l.b_qkv, 3 * C, C, C);
         if (!pl->f32) repack_qkv_hp_kernel<<<296, 64, 0, st>>>(l.w_qkv, l.b_qkv, l.w_qkv_hp, l.b_qkv_hp, C);
         pack(b[4], l.w_proj, C, C, C);  copy(b[5], l.b_proj, C);
-        copy(b[6], l.ln2_g, C);  copy(b[7], l.ln2_b, C);
-        pack(b[8], l.w_fc1, C, C, C);  copy(b[9], l.b_fc1, C);
+        ln_vectors(b[6], b[7], l.ln2_g, l.ln2_b);
+        if (pl->f32) copy(b[9], l.b_fc1, C);
+        else fold(b[8], b[6], b[7], b[9], l.w_fc1, l.b_fc1, C, C, C);
         pack(b[10], l.w_fc2, C, C, C);  copy(b[11], l.b_fc2, C);
     }
     const float* const* e = t + 5 + 12 * pl->sh.depth;
-    copy(e[0], pl->lnf_g, C);  copy(e[1], pl->lnf_b, C);
-    pack(e[2], pl->w_head, P, C, C);  copy(e[3], pl->b_head, P);
+    ln_vectors(e[0], e[1], pl->lnf_g, pl->lnf_b);
+    if (pl->f32) copy(e[3], pl->b_head, P);
+    else fold(e[2], e[0], e[1], e[3], pl->w_head, pl->b_head, P, C, C);
     CK(cudaGetLastError());
     // The step-path kernels are launched with programmatic dependent launch and read weights (bias, LayerNorm affine)
     // in their prologue, BEFORE they wait for their predecessor.  Packing is rare, so make it a full stop: once this
@@ -924,8 +940,7 @@ static int enqueue_predictor(ddc_plan* pl, const float* x, int B, const int* t_i
         if (block_tail_usable(M, C, pl->bn_row)) {
             BlockTailParams bt{};
             bt.M = M; bt.C = C; bt.ln_eps = 1e-5f;
-            bt.b_proj = l.b_proj; bt.ln2_g = l.ln2_g; bt.ln2_b = l.ln2_b; bt.b_fc1 = l.b_fc1; bt.b_fc2 = l.b_fc2;
-            bt.lnn_g = lnn_g; bt.lnn_b = lnn_b;
+            bt.b_proj = l.b_proj; bt.b_fc1 = l.b_fc1; bt.b_fc2 = l.b_fc2;
             if (f16) TRY((launch_block_tail_inst<true>(pl->tm_O, l.tm_proj[1], l.tm_fc1_tail, l.tm_fc2[1], pl->tm_Xld, pl->st_X, pl->st_XN, bt, st)));
             else TRY((launch_block_tail_inst<false>(pl->tm_O, l.tm_proj[1], l.tm_fc1_tail, l.tm_fc2[1], pl->tm_Xld, pl->st_X, pl->st_XN, bt, st)));
             MARK(KC_PROJ);
@@ -1356,11 +1371,9 @@ extern "C" int ddc_k_embed(int32_t fmt, int32_t batch, int32_t L, int32_t C, int
 }
 
 extern "C" int ddc_k_block_tail(int32_t fmt, int32_t M, int32_t C, const void* O, const void* Wproj, const float* b_proj,
-                                const float* ln2_g, const float* ln2_b, const void* Wfc1, const float* b_fc1,
-                                const void* Wfc2, const float* b_fc2, const float* lnn_g, const float* lnn_b, float* x,
-                                void* xn, void* stream) {
-    if (!O || !Wproj || !b_proj || !ln2_g || !ln2_b || !Wfc1 || !b_fc1 || !Wfc2 || !b_fc2 || !lnn_g || !lnn_b || !x || !xn)
-        return fail(DDC_E_INVALID, "NULL tensor");
+                                const void* Wfc1, const float* b_fc1, const void* Wfc2, const float* b_fc2, float* x, void* xn,
+                                void* stream) {
+    if (!O || !Wproj || !b_proj || !Wfc1 || !b_fc1 || !Wfc2 || !b_fc2 || !x || !xn) return fail(DDC_E_INVALID, "NULL tensor");
     if (M < 129 || C % 128 != 0 || C > 384 || C <= 0)
         return fail(DDC_E_INVALID, "block tail needs M > 128 and embed_dim in {128, 256, 384} (M=%d C=%d)", M, C);
     const uint64_t Mp = (static_cast<uint64_t>(M) + G2_BM - 1) / G2_BM * G2_BM;
@@ -1374,7 +1387,7 @@ extern "C" int ddc_k_block_tail(int32_t fmt, int32_t M, int32_t C, const void* O
     TRY(make_tmap(&tmXN, false, xn, M, C, G2_BM));
     BlockTailParams bt{};
     bt.M = M; bt.C = C; bt.ln_eps = 1e-5f;
-    bt.b_proj = b_proj; bt.ln2_g = ln2_g; bt.ln2_b = ln2_b; bt.b_fc1 = b_fc1; bt.b_fc2 = b_fc2; bt.lnn_g = lnn_g; bt.lnn_b = lnn_b;
+    bt.b_proj = b_proj; bt.b_fc1 = b_fc1; bt.b_fc2 = b_fc2;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (fmt == 1) return launch_block_tail_inst<true>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, bt, st);
     return launch_block_tail_inst<false>(tmO, tmWp, tmW1, tmW2, tmXld, tmXst, tmXN, bt, st);

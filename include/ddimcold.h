@@ -196,12 +196,13 @@ int ddc_k_gemm_resid_ln(int32_t fmt, int32_t M, int32_t C, int32_t K, const void
                         const float* ln_g, const float* ln_b, void* xn, void* stream);
 
 /* Fused tail of a transformer block (reference ViT.py:136-137 with Mlp.forward :84-90 and the LayerNorm that
- * follows, :133 / :212):  x += O Wproj^T + b_proj;  h = gelu_erf(LayerNorm2(x) Wfc1^T + b_fc1);
- * x += h Wfc2^T + b_fc2 (fp32, in place);  xn = 16-bit LayerNorm_next(x).  O: 16-bit [m_pad, C]; W*: 16-bit [C, C];
- * x: fp32 [m_pad, C]; xn: 16-bit [M, C]; C in {128, 256, 384}; M > 128. */
-int ddc_k_block_tail(int32_t fmt, int32_t M, int32_t C, const void* O, const void* Wproj, const float* b_proj,
-                     const float* ln2_g, const float* ln2_b, const void* Wfc1, const float* b_fc1, const void* Wfc2,
-                     const float* b_fc2, const float* lnn_g, const float* lnn_b, float* x, void* xn, void* stream);
+ * follows, :133 / :212):  x += O Wproj^T + b_proj;  h = gelu_erf(N(x) Wfc1^T + b_fc1);  x += h Wfc2^T + b_fc2 (fp32, in
+ * place);  xn = 16-bit N(x), where N is LayerNorm WITHOUT its affine part (eps 1e-5): the caller folds norm2's gamma / beta
+ * into Wfc1 / b_fc1 (W o gamma, b + W beta) and the following LayerNorm's into the Linear that consumes xn, as
+ * ddc_pack_weights does for a whole model.  O: 16-bit [m_pad, C]; W*: 16-bit [C, C]; x: fp32 [m_pad, C]; xn: 16-bit [M, C];
+ * C in {128, 256, 384}; M > 128. */
+int ddc_k_block_tail(int32_t fmt, int32_t M, int32_t C, const void* O, const void* Wproj, const float* b_proj, const void* Wfc1,
+                     const float* b_fc1, const void* Wfc2, const float* b_fc2, float* x, void* xn, void* stream);
 
 /* softmax(q k^T / sqrt(d)) v per (image, head) (reference ViT.py:107-114).
  * qkv: bf16 [B*L, 3C] (column s*C + head*d + e); out: bf16 [B*L, C]. */
