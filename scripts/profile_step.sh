@@ -8,14 +8,14 @@ CMD="python bench.py --steps 1 --warmup 3 --lean --no-cpu-baseline --k 500"
 set -x
 $CMD > gpurun_out/${TAG}_plain.log 2>&1 || exit 1          # the profiled command must pass without the profiler first
 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
-# one whole step = the launches from the last-but-one patchify to the next one
+# one whole step = the launches from the last-but-one unpatchify + DDIM launch to the next one (patchify runs once per loop)
 SKIP=$(python - <<PY
 import csv
 rows = [r for r in csv.reader(open("gpurun_out/${TAG}_launches.csv")) if len(r) > 10]
 ki = rows[0].index("Kernel Name")
 names = [r[ki] for r in rows[1:]]
-idx = [i for i, n in enumerate(names) if "patchify" in n]
-print(idx[-2], idx[-1] - idx[-2])
+idx = [i for i, n in enumerate(names) if "head_ddim" in n]
+print(idx[-2] + 1, min(idx[-1] - idx[-2], 40))
 PY
 )
 set -- $SKIP
