@@ -275,7 +275,9 @@ attention_stream_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restr
 // ---------------------------------------------------------------------------- one CTA per (image, head)
 inline size_t att_head_smem_bytes(int L, int D, int KC) {
     const int lk = (L + KC - 1) / KC * KC;
-    return static_cast<size_t>(2) * lk * (D + 8) * 2;
+    // K, V, and (head_dim 64) a warp-private output staging tile; with head_dim 32 the staging measured slower (S3: 566 ->
+    // 704 us: K and V of 626 tokens leave no room for it beside a second CTA on the SM)
+    return static_cast<size_t>(2) * lk * (D + 8) * 2 + (D == 64 ? static_cast<size_t>(ATT_MAX_WARPS) * 16 * (D + 8) * 2 : 0);
 }
 
 template <int D, int KC, bool F16>
@@ -329,14 +331,33 @@ attention_head_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, int 
         }
         float o[DT][4];
         attend_qtile<D, KC, F16, false, RS, false>(qa, Ks, Vs, L, lk_pad, scale_log2e, lane, o);
+        // The fragments hold 4-byte pieces of 16 rows: stored from here an instruction would write 8 rows x 16 B.  Through a
+        // warp-private [16 rows x D] tile (row pitch padded by 16 B) every store instruction writes whole 16-byte chunks of
+        // full rows instead (uncoalesced stores clog the SM's load/store path, see qkv_attn_tc.cuh).
         bf16* ob = out + static_cast<size_t>(img) * L * C + head * D;
+        if (D != 64) {
+#pragma unroll
+            for (int dt = 0; dt < DT; ++dt) {
+                if (r0 < L)
+                    *reinterpret_cast<uint32_t*>(ob + static_cast<size_t>(r0) * C + dt * 8 + 2 * t) = pack2<F16>(o[dt][0], o[dt][1]);
+                if (r1 < L)
+                    *reinterpret_cast<uint32_t*>(ob + static_cast<size_t>(r1) * C + dt * 8 + 2 * t) = pack2<F16>(o[dt][2], o[dt][3]);
+            }
+            continue;
+        }
+        uint8_t* stg = Vs + static_cast<size_t>(lk_pad) * RS + static_cast<size_t>(warp) * 16 * RS;
 #pragma unroll
         for (int dt = 0; dt < DT; ++dt) {
-            if (r0 < L)
-                *reinterpret_cast<uint32_t*>(ob + static_cast<size_t>(r0) * C + dt * 8 + 2 * t) = pack2<F16>(o[dt][0], o[dt][1]);
-            if (r1 < L)
-                *reinterpret_cast<uint32_t*>(ob + static_cast<size_t>(r1) * C + dt * 8 + 2 * t) = pack2<F16>(o[dt][2], o[dt][3]);
+            *reinterpret_cast<uint32_t*>(stg + g * RS + dt * 16 + 4 * t) = pack2<F16>(o[dt][0], o[dt][1]);
+            *reinterpret_cast<uint32_t*>(stg + (g + 8) * RS + dt * 16 + 4 * t) = pack2<F16>(o[dt][2], o[dt][3]);
         }
+        __syncwarp();
+        for (int i = lane; i < 16 * CPR; i += 32) {
+            const int rr = i / CPR, ch = i - rr * CPR;
+            if (q0 + rr < L)
+                *reinterpret_cast<uint4*>(ob + static_cast<size_t>(q0 + rr) * C + ch * 8) = *reinterpret_cast<const uint4*>(stg + rr * RS + ch * 16);
+        }
+        __syncwarp();
     }
 }
 
