@@ -1,7 +1,7 @@
 """Benchmark of the DDIM sampling hot path (BASELINE.json metric: DDIM images/sec (N, k)).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--shape s1|s2|s3] [--format fp16|bf16]
-                    [--scaling weak|strong] [--config 3|5] [--lean]
+                    [--scaling weak|strong] [--config 3|5] [--sweep] [--lean]
 
 One "step" of this benchmark is one complete pass of the hot path over one batch: the whole k-strided DDIM loop
 (k=20 -> 100 predictor evaluations + updates) for `--batch` images per GPU of the workload BASELINE.json quotes its
@@ -598,6 +598,90 @@ def run_strong(args):
         dist.destroy_process_group()
 
 
+# ------------------------------------------------------------------------------------------------ batch / step sweep
+def run_sweep(args):
+    """BASELINE config #4: N = 1..8192 images, k in {50, 10, 1}, each (N, k) sharded over the ranks through
+    `sample_sharded` (ranks whose slice is empty sit the run out), host noise in and images back in one shared
+    page-locked host buffer.  One JSON line: a row per (N, k) with images/s and ms per denoise step (max over ranks);
+    the k = 50 rows are also checked bit-identical against the same problem on rank 0's GPU alone."""
+    import torch.distributed as dist
+    from ddim_cold_b200 import SharedHostImages, sample_sharded, shard_bounds, synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    model, sh, _ = make_model("s1", dev, args.format)
+    H = SHAPES["s1"]["img"]
+    img_shape = (3, H, H)
+    n_list = [1, 8, 64, 512, 2048, 8192]
+    noise_all = torch.from_numpy(synth.synth_noise((max(n_list),) + img_shape, seed=123))
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+
+    rows, clk = [], None
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    for k in (50, 10, 1):
+        steps = len(range(sh.total_steps - 1, 0, -k))
+        for N in n_list:
+            noise = noise_all[:N]
+            shared = SharedHostImages(N, img_shape)
+            lo, hi = shard_bounds(N, world, rank)
+
+            def local_run(ns):
+                with contextlib.redirect_stdout(sys.stderr):
+                    return model.sampler(dev, k, ns.shape[0], noise=ns, return_on_device=True)
+
+            def one_pass():
+                res = sample_sharded(lambda ns: local_run(ns.pin_memory()), N, img_shape, noise=noise, gather=False)
+                if hi > lo:
+                    shared.put(lo, res)
+                return shared.wait_all()
+
+            one_pass()                                  # plan, graph, page-locked buffers
+            best = None
+            for _ in range(2 if k > 1 else 1):
+                barrier()
+                t0 = time.perf_counter()
+                imgs = one_pass()
+                barrier()
+                ms = (time.perf_counter() - t0) * 1e3
+                if world > 1:
+                    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                    ms = float(t.item())
+                best = ms if best is None else min(best, ms)
+            row = {"N": N, "k": k, "denoise_steps": steps, "images_per_rank": -(-N // world), "ranks_used": min(world, N),
+                   "ms": best, "images_per_s": N / (best / 1e3), "ms_per_denoise_step": best / steps}
+            if rank == 0 and k == 50 and world > 1:
+                single = local_run(noise.pin_memory()).cpu()
+                row["bit_identical_to_1gpu"] = bool(torch.equal(single, imgs))
+                assert row["bit_identical_to_1gpu"], f"sharded N={N} differs from the single-GPU result"
+            rows.append(row)
+            barrier()
+            shared.close()
+    if rank == 0:
+        clk = clocks.stop()
+        print(json.dumps({
+            "metric": "DDIM images/sec over a batch / step-jump sweep", "unit": "images/s", "n_gpus": world,
+            "scaling": "strong", "dtype": args.format, "data": "synthetic", "higher_is_better": True,
+            "config": {"workload": f"config #4: {SHAPES['s1']['desc']}, N in {n_list}, k in [50, 10, 1]",
+                       "parallelism": f"sample_sharded over {world} rank(s), no step-path collective",
+                       "timed": "host noise in -> images on the host (public API), wall clock between barriers, max over "
+                                "ranks, best of 2 passes (1 at k = 1) after one warm-up pass"},
+            "rows": rows, "clocks": clk}), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def _launches(model, dev, batch):
     from ddim_cold_b200 import _lib
     return _lib.load().ddc_launches_per_step(model._plan(dev, max(1, batch)).handle)
@@ -616,6 +700,7 @@ def main():
                     help="tensor-core operand format (fp16 meets the 1e-2 eps bound; bf16 is the opt-in that misses it)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--config", type=int, default=3, choices=[3, 5], help="--scaling strong: BASELINE.json config to run")
+    ap.add_argument("--sweep", action="store_true", help="BASELINE config #4: batch / step-jump sweep over all ranks")
     ap.add_argument("--lean", action="store_true", help="headline only: skip parity / alt_format / other_shapes / stock torch")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -626,6 +711,8 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     if args.impl == "reference":
         return run_reference(args)
+    if args.sweep:
+        return run_sweep(args)
     if args.scaling == "strong":
         return run_strong(args)
     return run_weak(args)
