@@ -41,6 +41,7 @@ template <int D> struct FaCfg {
     static constexpr int NV = D == 64 ? 3 : 4;         // V ring stages (a V chunk lives until the softmax of its chunk is done)
 };
 constexpr int FA_TMEM_W = 224;             // TMEM columns per warpgroup: S 128, O 64, row sums 32
+constexpr float FA_MAX_SLACK = 8.f;        // see the softmax warps
 constexpr int FA_SIDE_MAX = 8;             // remainder rows handed to the CUDA-core kernel
 constexpr int FA_SMEM_BYTES = 1024 + 13 * FA_TILE + 2048 + 2048 + 512;
 
@@ -317,7 +318,10 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tm,       // qkv [rows, 
                 named_bar_sync(1 + w, 256);                     // both halves of tile w have published their maxima
                 mx = fmaxf(mx, *other_max) * sc;                // scaled (log2) domain; scale > 0; identical in both halves
                 float alpha = 1.f;
-                if (mx > m) { alpha = ex2_approx(m - mx); m = mx; }         // first chunk: 2^(-inf) = 0, unused
+                // The running maximum only moves when a row's scores outgrow it by more than FA_MAX_SLACK (log2 units): P then
+                // stays below 2^FA_MAX_SLACK, exact for the quotient P V / P 1 and well inside 16-bit range, and O is not
+                // rescaled for the usual small drift of a row maximum from chunk to chunk (first chunk: m = -inf, always taken)
+                if (mx > m + FA_MAX_SLACK) { alpha = ex2_approx(m - mx); m = mx; }
                 const bool rescale = c > 0 && __any_sync(0xffffffffu, alpha != 1.f);
                 FA_STAMP(1 + w, sfull_it - 1, 3);
                 if (c > 0) {                        // P*V of the previous chunk is done: P may be overwritten, O is stable
