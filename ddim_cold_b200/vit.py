@@ -261,6 +261,10 @@ class DiffusionVisionTransformer(nn.Module):
         on_dev = x_init.device.type == "cuda"
         if on_dev and x_init.device != dev:
             raise RuntimeError(f"initial state lives on {x_init.device}, sampler asked for {dev}")
+        if N == 0:          # an empty batch is legal in the reference (every op runs on [0, ...] tensors): nothing to launch
+            return (torch.empty((0,) + img, dtype=torch.float32, device=dev if keep_on_device else "cpu"),
+                    torch.empty((n_steps, 0) + img, dtype=torch.float32) if want_seq else None,
+                    torch.empty((n_steps, 0) + img, dtype=torch.float32) if want_eps else None)
         src = x_init.detach().to(torch.float32).contiguous()
         if not on_dev and not src.is_pinned():
             src = src.pin_memory()

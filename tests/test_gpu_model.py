@@ -112,6 +112,29 @@ def test_deterministic_and_batch_invariant(tiny):
     assert torch.equal(a, b) and torch.equal(a[1:2], c)
 
 
+def test_ragged_chunks_and_empty_batch(tiny):
+    """Batches above `max_batch_per_call` run as chunks (here 3 + 3 + 1) overlapped on two streams: every sample must come
+    out bit-identical to the single-call run, for the sampler and for the per-step sequence.  An empty batch is legal in
+    the reference (ViT.py:224 draws a [0,3,H,W] tensor and every op accepts it) and returns an empty result."""
+    g, sd, m = tiny
+    x = torch.from_numpy(np.concatenate([g["samp100_xT"]] * 3)[:7].copy())
+    whole = m.sampler("cuda", 100, 7, noise=x)
+    seq_whole = m.diffusion_sequence("cuda", 500, 7, noise=x)
+    from oracle import ddim_oracle as O
+    m2 = build(O.TINY, sd)
+    m2.max_batch_per_call = 3
+    parts = m2.sampler("cuda", 100, 7, noise=x)
+    seq_parts = m2.diffusion_sequence("cuda", 500, 7, noise=x)
+    assert torch.equal(whole, parts)
+    assert len(seq_whole) == len(seq_parts) and all(torch.equal(a, b) for a, b in zip(seq_whole, seq_parts))
+    on_dev = m2.sampler("cuda", 100, 7, noise=x.cuda(), return_on_device=True)
+    assert on_dev.is_cuda and torch.equal(on_dev.cpu(), whole)
+    empty = m.sampler("cuda", 100, 0, noise=x[:0])
+    assert tuple(empty.shape) == (0, 3) + tuple(x.shape[2:]) and empty.dtype == torch.float32
+    seq = m.diffusion_sequence("cuda", 500, 0, noise=x[:0])
+    assert len(seq) == len(seq_whole) and all(tuple(t.shape) == tuple(empty.shape) for t in seq)
+
+
 def test_batch_invariant_on_the_fused_path():
     """The same check on a shape that takes the fused block tail, the tcgen05 GEMM pair kernels and the 65-token
     attention (embed 128, L = 65): one sample alone (a single, half-empty tile pair) == the same sample in a batch."""
