@@ -428,20 +428,18 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
             // the O tile in Abuf completed before proj_bar[NB-1] fired.
             for (int c = hf; c < C / 64; c += NG) {
                 uint8_t* kblk = abuf + static_cast<size_t>(c) * G2_A_KB_BYTES;
+                float v[64];                       // the K block's 64 columns: both loads in flight before the one wait
+                tmem_ld32_nowait(lane_taddr + c * 64, v);
+                tmem_ld32_nowait(lane_taddr + c * 64 + 32, v + 32);
+                tmem_ld_wait64(v);
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    float v[32];
-                    const int n0 = c * 64 + 32 * h;
-                    tmem_ld32(lane_taddr + n0, v);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        uint4 o;
-                        o.x = pack2<F16>(fmaf(v[8 * j], rstd, nmr), fmaf(v[8 * j + 1], rstd, nmr));
-                        o.y = pack2<F16>(fmaf(v[8 * j + 2], rstd, nmr), fmaf(v[8 * j + 3], rstd, nmr));
-                        o.z = pack2<F16>(fmaf(v[8 * j + 4], rstd, nmr), fmaf(v[8 * j + 5], rstd, nmr));
-                        o.w = pack2<F16>(fmaf(v[8 * j + 6], rstd, nmr), fmaf(v[8 * j + 7], rstd, nmr));
-                        *reinterpret_cast<uint4*>(kblk + slot_off(trow, 4 * h + j)) = o;
-                    }
+                for (int j = 0; j < 8; ++j) {
+                    uint4 o;
+                    o.x = pack2<F16>(fmaf(v[8 * j], rstd, nmr), fmaf(v[8 * j + 1], rstd, nmr));
+                    o.y = pack2<F16>(fmaf(v[8 * j + 2], rstd, nmr), fmaf(v[8 * j + 3], rstd, nmr));
+                    o.z = pack2<F16>(fmaf(v[8 * j + 4], rstd, nmr), fmaf(v[8 * j + 5], rstd, nmr));
+                    o.w = pack2<F16>(fmaf(v[8 * j + 6], rstd, nmr), fmaf(v[8 * j + 7], rstd, nmr));
+                    *reinterpret_cast<uint4*>(kblk + slot_off(trow, j)) = o;
                 }
                 fence_proxy_async_smem();          // generic writes -> visible to the tensor core's operand reads
                 tc_fence_before();
@@ -461,9 +459,15 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 // read this thread's accumulator columns, then hand the accumulator back at once: fc1 of the next
                 // hidden block overlaps the GELU below
                 float vv[HW / 32][32];
+                if constexpr (HW == 64) {          // both loads in flight before the one wait
+                    tmem_ld32_nowait(lane_taddr + static_cast<uint32_t>(C) + hf * HW, vv[0]);
+                    tmem_ld32_nowait(lane_taddr + static_cast<uint32_t>(C) + hf * HW + 32, vv[1]);
+                    tmem_ld_wait64(&vv[0][0]);
+                } else {
 #pragma unroll
-                for (int h = 0; h < HW / 32; ++h)
-                    tmem_ld32(lane_taddr + static_cast<uint32_t>(C) + hf * HW + 32 * h, vv[h]);
+                    for (int h = 0; h < HW / 32; ++h)
+                        tmem_ld32(lane_taddr + static_cast<uint32_t>(C) + hf * HW + 32 * h, vv[h]);
+                }
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive_leader(t1free_bar);
@@ -543,13 +547,14 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                 uint8_t* slot = gslots + (ri % SL) * G2_GSLOT_BYTES;
                 if (gleader) bulk_wait_read<SL - 1>();   // the store that last used this slot has read it
                 named_bar_sync(gbar, 128);
+                {
+                    float v[64];                   // both loads in flight before the one wait
+                    const int n0 = c * 64;
+                    tmem_ld32_nowait(lane_taddr + n0, v);
+                    tmem_ld32_nowait(lane_taddr + n0 + 32, v + 32);
+                    tmem_ld_wait64(v);
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    float v[32];
-                    const int n0 = c * 64 + 32 * h;
-                    tmem_ld32(lane_taddr + n0, v);
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
+                    for (int j = 0; j < 8; ++j) {
                         const float4 a0 = *reinterpret_cast<const float4*>(s_bfc2 + n0 + 8 * j);
                         const float4 a1 = *reinterpret_cast<const float4*>(s_bfc2 + n0 + 8 * j + 4);
                         uint4 o;
@@ -557,7 +562,7 @@ block_tail_kernel(const __grid_constant__ CUtensorMap tmO,      // O      [Mpad,
                         o.y = pack2<F16>(fmaf(v[8 * j + 2] + a0.z, rstd, nmr), fmaf(v[8 * j + 3] + a0.w, rstd, nmr));
                         o.z = pack2<F16>(fmaf(v[8 * j + 4] + a1.x, rstd, nmr), fmaf(v[8 * j + 5] + a1.y, rstd, nmr));
                         o.w = pack2<F16>(fmaf(v[8 * j + 6] + a1.z, rstd, nmr), fmaf(v[8 * j + 7] + a1.w, rstd, nmr));
-                        *reinterpret_cast<uint4*>(slot + slot_off(trow, 4 * h + j)) = o;
+                        *reinterpret_cast<uint4*>(slot + slot_off(trow, j)) = o;
                     }
                 }
                 // the two 64-column halves of N tile c / 2 belong to two groups: once both are read out, the next tile's
