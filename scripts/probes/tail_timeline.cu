@@ -15,7 +15,7 @@ int main() {
         make_tmap(&tmW2, false, W2, C, C, 64) || make_tmap(&tmXld, true, X, Mp, C, G2_BM) || make_tmap(&tmXst, true, X, M, C, G2_BM) ||
         make_tmap(&tmXN, false, XN, M, C, G2_BM)) { printf("%s\n", ddc_last_error()); return 1; }
     BlockTailParams bt{};
-    bt.M = M; bt.C = C; bt.ln_eps = 1e-5f; bt.b_proj = bt.ln2_g = bt.ln2_b = bt.b_fc1 = bt.b_fc2 = bt.lnn_g = bt.lnn_b = v;
+    bt.M = M; bt.C = C; bt.ln_eps = 1e-5f; bt.b_proj = bt.b_fc1 = bt.b_fc2 = v;
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     for (int rep = 0; rep < 3; ++rep) {
         cudaMemset(dbg, 0, 3 * 64 * 8);
